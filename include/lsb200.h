@@ -1,0 +1,102 @@
+/*
+ * lsb200.h — kernel-level C ABI of the B200 executor core (libgpu_mega_ag_runner.so).
+ *
+ * This is the thin C layer the host runtime (and the reference-facing runner in
+ * lattisense_gpu_runner.h) calls CUDA through.  Each entry point names the reference interface it
+ * stands in for; paths are relative to the reference tree (cipherflow-fhe/lattisense @ 88bf833).
+ *
+ * Conventions (reference ABI, abi/c_types.h:26-60 flattened into contiguous device arrays):
+ *   - residues are uint64_t in [0, q_i); limbs ordered q_0..q_level, keys then p_0..p_{k-1}
+ *     (plug-in/lattigo/acc/c_struct_import_export.go:41-59)
+ *   - ciphertext  : [degree+1][level+1][N]
+ *   - eval key    : [beta][2][key_level+1+k][N], beta = ceil((key_level+1)/k), NTT domain, Montgomery removed
+ *   - CKKS ciphertexts/plaintexts are in the (Lattigo) NTT domain, BFV ones in the coefficient domain
+ *   - a batch is `batch` such blocks at a constant stride (`*_stride` words; 0 = densely packed)
+ *   - all pointers named d_* are DEVICE pointers on the context's GPU; `stream` is a cudaStream_t
+ *     (NULL = default stream).  Calls are asynchronous on that stream unless stated otherwise.
+ *   - every function returning int returns 0 on success, non-zero on failure (message via
+ *     lsb_last_error); there is no CPU fallback: without a CUDA device context creation fails.
+ */
+#ifndef LSB200_H
+#define LSB200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct lsb_context_st* lsb_context_t;
+
+enum { LSB_SCHEME_BFV = 0, LSB_SCHEME_CKKS = 1 };
+
+/* Last error message of the calling thread (empty string if none). */
+const char* lsb_last_error(void);
+/* Library version string. */
+const char* lsb_version(void);
+
+/* init_gpu_context (mega_ag_runners/gpu/gpu_wrapper.cu:53-138): modulus chain Q = q[0..nq), P = p[0..np),
+ * plaintext modulus t (BFV; 0 for CKKS), NTT tables.  Built once and reused (the reference rebuilds per run). */
+lsb_context_t lsb_context_create(int device, int scheme, int log_n, const uint64_t* q, int nq, const uint64_t* p,
+                                 int np, uint64_t t);
+void lsb_context_destroy(lsb_context_t ctx);
+int lsb_context_num_moduli(lsb_context_t ctx);           /* Q, P and (BFV) the auxiliary QMul basis */
+uint64_t lsb_context_modulus(lsb_context_t ctx, int i);
+int lsb_context_level_qmul(lsb_context_t ctx, int level); /* BFV: index of the last QMul prime used at `level` */
+
+/* Device memory + transfers (gpu_abi_bridge_executors.h:60-191 does one cudaMemcpyAsync per limb). */
+uint64_t* lsb_device_alloc(lsb_context_t ctx, size_t words);
+void lsb_device_free(lsb_context_t ctx, uint64_t* d_ptr);
+int lsb_upload(lsb_context_t ctx, uint64_t* d_dst, const uint64_t* h_src, size_t words, void* stream);
+int lsb_download(lsb_context_t ctx, uint64_t* h_dst, const uint64_t* d_src, size_t words, void* stream);
+int lsb_stream_sync(lsb_context_t ctx, void* stream);
+/* Max batch items per scratch pass (0 = automatic, sized to keep scratch L2-resident). */
+void lsb_set_chunk(lsb_context_t ctx, int chunk);
+
+/* Batched negacyclic NTT / INTT over `rows` limbs per item; limb r uses modulus index mod_idx[r % period].
+ * Stands in for the HEonGPU NTT under every operator; ordering = Lattigo ring.NTT / ring.InvNTT. */
+int lsb_ntt(lsb_context_t ctx, const uint64_t* d_in, uint64_t* d_out, int rows, const int* mod_idx, int period,
+            int inverse, int batch, void* stream);
+
+/* bind_gpu_mult, ct x ct (mega_ag_executors_gpu.cu:177-227; CPU twin mega_ag_executors_cpu.cpp:186,230). */
+int lsb_mult(lsb_context_t ctx, int level, const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_out3, int batch,
+             void* stream);
+/* bind_gpu_relin (mega_ag_executors_gpu.cu:229-238; CPU :236-242). */
+int lsb_relin(lsb_context_t ctx, int level, const uint64_t* d_ct3, const uint64_t* d_rlk, int key_level,
+              uint64_t* d_out2, int batch, void* stream);
+/* bind_gpu_rescale (mega_ag_executors_gpu.cu:240-248; CPU :244-255). */
+int lsb_rescale(lsb_context_t ctx, int level, int npoly, const uint64_t* d_in, uint64_t* d_out, int batch,
+                void* stream);
+/* bind_gpu_drop_level (mega_ag_executors_gpu.cu:250-262). */
+int lsb_drop_level(lsb_context_t ctx, int level, int npoly, const uint64_t* d_in, uint64_t* d_out, int batch,
+                   void* stream);
+/* bind_gpu_rotate_col / bind_gpu_rotate_row (mega_ag_executors_gpu.cu:264-292): automorphism X -> X^gal
+ * (gal = 5^step mod 2N for columns, 2N-1 for rows / conjugate; frontend/custom_task.py:139-145) + key-switch. */
+int lsb_rotate(lsb_context_t ctx, int level, const uint64_t* d_ct, const uint64_t* d_glk, int key_level,
+               uint64_t galois_element, uint64_t* d_out, int batch, void* stream);
+/* bind_gpu_add / sub / neg (mega_ag_executors_gpu.cu:71-175). */
+int lsb_add(lsb_context_t ctx, int level, int npoly, const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_out,
+            int batch, void* stream);
+int lsb_sub(lsb_context_t ctx, int level, int npoly, const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_out,
+            int batch, void* stream);
+int lsb_neg(lsb_context_t ctx, int level, int npoly, const uint64_t* d_a, uint64_t* d_out, int batch, void* stream);
+/* ct +/- pt, ct +/- pt_ringt, ct x pt_mul, ct x pt_ringt (plain branches, mega_ag_executors_gpu.cu:92-161,189-214). */
+int lsb_add_plain(lsb_context_t ctx, int level, int npoly, const uint64_t* d_ct, const uint64_t* d_pt,
+                  uint64_t* d_out, int subtract, int batch, void* stream);
+int lsb_add_plain_ringt(lsb_context_t ctx, int level, int npoly, const uint64_t* d_ct, const uint64_t* d_pt,
+                        uint64_t* d_out, int subtract, int batch, void* stream);
+int lsb_mul_plain(lsb_context_t ctx, int level, int npoly, const uint64_t* d_ct, const uint64_t* d_pt,
+                  uint64_t* d_out, int batch, void* stream);
+int lsb_mul_plain_ringt(lsb_context_t ctx, int level, int npoly, const uint64_t* d_ct, const uint64_t* d_pt,
+                        uint64_t* d_out, int batch, void* stream);
+/* Fused chains the runner substitutes for mult -> relin (-> rescale) node sequences
+ * (frontend mult_relin, custom_task.py:1286; benchmark graphs examples/benchmark_gpu/benchmark_gpu.cpp:26-78). */
+int lsb_mult_relin(lsb_context_t ctx, int level, const uint64_t* d_a, const uint64_t* d_b, const uint64_t* d_rlk,
+                   int key_level, uint64_t* d_out2, int batch, void* stream);
+int lsb_mult_relin_rescale(lsb_context_t ctx, int level, const uint64_t* d_a, const uint64_t* d_b,
+                           const uint64_t* d_rlk, int key_level, uint64_t* d_out2, int batch, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LSB200_H */

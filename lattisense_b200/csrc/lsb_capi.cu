@@ -1,0 +1,227 @@
+// extern "C" surface declared in include/lsb200.h.
+#include <mutex>
+#include <cstring>
+#include "../../include/lsb200.h"
+#include "lsb_ops.h"
+
+using namespace lsb;
+
+struct lsb_context_st {
+    std::unique_ptr<Context> c;
+    std::mutex mu;  // serialises users of the default workspace
+    int chunk = 0;
+};
+
+static thread_local std::string g_err;
+
+#define LSB_API_BEGIN \
+    g_err.clear();    \
+    try {
+#define LSB_API_END(fail)                 \
+    }                                     \
+    catch (const std::exception& ex) {    \
+        g_err = ex.what();                \
+        return fail;                      \
+    }                                     \
+    catch (...) {                         \
+        g_err = "lsb: unknown exception"; \
+        return fail;                      \
+    }
+
+template <class F>
+static int run_op(lsb_context_t h, void* stream, F&& f) {
+    LSB_API_BEGIN
+    LSB_CHECK(h && h->c, "lsb: null context");
+    std::lock_guard<std::mutex> lk(h->mu);
+    OpEnv e{*h->c, h->c->default_workspace(), (cudaStream_t)stream, h->chunk};
+    f(e);
+    return 0;
+    LSB_API_END(1)
+}
+
+static BatchPtr dense(const uint64_t* p, size_t words) { return bp_strided(p, words); }
+
+extern "C" {
+
+const char* lsb_last_error(void) { return g_err.c_str(); }
+const char* lsb_version(void) { return "lattisense-b200 0.1 (sm_100a)"; }
+
+lsb_context_t lsb_context_create(int device, int scheme, int log_n, const uint64_t* q, int nq, const uint64_t* p,
+                                 int np, uint64_t t) {
+    LSB_API_BEGIN
+    int ndev = 0;
+    cudaError_t err = cudaGetDeviceCount(&ndev);
+    if (err != cudaSuccess || ndev == 0)
+        throw std::runtime_error(std::string("lsb: no CUDA device available (") + cudaGetErrorString(err) +
+                                 "); this library has no CPU fallback");
+    LSB_CHECK(device >= 0 && device < ndev, "lsb: device index out of range");
+    auto* h = new lsb_context_st();
+    try {
+        h->c.reset(new Context(device, scheme, log_n, q, nq, p, np, t));
+    } catch (...) {
+        delete h;
+        throw;
+    }
+    return h;
+    LSB_API_END(nullptr)
+}
+void lsb_context_destroy(lsb_context_t h) { delete h; }
+int lsb_context_num_moduli(lsb_context_t h) { return h && h->c ? (int)h->c->moduli.size() : 0; }
+uint64_t lsb_context_modulus(lsb_context_t h, int i) {
+    return (h && h->c && i >= 0 && i < (int)h->c->moduli.size()) ? h->c->moduli[i] : 0;
+}
+int lsb_context_level_qmul(lsb_context_t h, int level) {
+    return (h && h->c && level >= 0 && level < (int)h->c->level_qmul.size()) ? h->c->level_qmul[level] : -1;
+}
+void lsb_set_chunk(lsb_context_t h, int chunk) {
+    if (h) h->chunk = chunk;
+}
+
+uint64_t* lsb_device_alloc(lsb_context_t h, size_t words) {
+    LSB_API_BEGIN
+    LSB_CHECK(h && h->c, "lsb: null context");
+    LSB_CUDA(cudaSetDevice(h->c->device));
+    void* p = nullptr;
+    LSB_CUDA(cudaMalloc(&p, words * sizeof(uint64_t)));
+    return (uint64_t*)p;
+    LSB_API_END(nullptr)
+}
+void lsb_device_free(lsb_context_t h, uint64_t* d) {
+    if (!h || !h->c || !d) return;
+    cudaSetDevice(h->c->device);
+    cudaFree(d);
+}
+int lsb_upload(lsb_context_t h, uint64_t* d_dst, const uint64_t* h_src, size_t words, void* stream) {
+    LSB_API_BEGIN
+    LSB_CHECK(h && h->c, "lsb: null context");
+    LSB_CUDA(cudaSetDevice(h->c->device));
+    LSB_CUDA(cudaMemcpyAsync(d_dst, h_src, words * 8, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    return 0;
+    LSB_API_END(1)
+}
+int lsb_download(lsb_context_t h, uint64_t* h_dst, const uint64_t* d_src, size_t words, void* stream) {
+    LSB_API_BEGIN
+    LSB_CHECK(h && h->c, "lsb: null context");
+    LSB_CUDA(cudaSetDevice(h->c->device));
+    LSB_CUDA(cudaMemcpyAsync(h_dst, d_src, words * 8, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    return 0;
+    LSB_API_END(1)
+}
+int lsb_stream_sync(lsb_context_t h, void* stream) {
+    LSB_API_BEGIN
+    LSB_CHECK(h && h->c, "lsb: null context");
+    LSB_CUDA(cudaSetDevice(h->c->device));
+    LSB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return 0;
+    LSB_API_END(1)
+}
+
+int lsb_ntt(lsb_context_t h, const uint64_t* d_in, uint64_t* d_out, int rows, const int* mod_idx, int period,
+            int inverse, int batch, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        const size_t w = (size_t)rows * e.c.N;
+        op_ntt(e, dense(d_in, w), dense(d_out, w), rows, mod_idx, period, inverse != 0, batch);
+    });
+}
+int lsb_mult(lsb_context_t h, int level, const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_out3, int batch,
+             void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        op_mult(e, level, dense(d_a, e.c.ct_words(level, 2)), dense(d_b, e.c.ct_words(level, 2)),
+                dense(d_out3, e.c.ct_words(level, 3)), batch);
+    });
+}
+int lsb_relin(lsb_context_t h, int level, const uint64_t* d_ct3, const uint64_t* d_rlk, int key_level,
+              uint64_t* d_out2, int batch, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        op_relin(e, level, dense(d_ct3, e.c.ct_words(level, 3)), d_rlk, key_level,
+                 dense(d_out2, e.c.ct_words(level, 2)), batch);
+    });
+}
+int lsb_rescale(lsb_context_t h, int level, int npoly, const uint64_t* d_in, uint64_t* d_out, int batch,
+                void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        op_rescale(e, level, npoly, dense(d_in, e.c.ct_words(level, npoly)),
+                   dense(d_out, e.c.ct_words(level - 1, npoly)), batch);
+    });
+}
+int lsb_drop_level(lsb_context_t h, int level, int npoly, const uint64_t* d_in, uint64_t* d_out, int batch,
+                   void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        op_drop_level(e, level, npoly, dense(d_in, e.c.ct_words(level, npoly)),
+                      dense(d_out, e.c.ct_words(level - 1, npoly)), batch);
+    });
+}
+int lsb_rotate(lsb_context_t h, int level, const uint64_t* d_ct, const uint64_t* d_glk, int key_level,
+               uint64_t galois_element, uint64_t* d_out, int batch, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        op_rotate(e, level, dense(d_ct, e.c.ct_words(level, 2)), d_glk, key_level, galois_element,
+                  dense(d_out, e.c.ct_words(level, 2)), batch);
+    });
+}
+int lsb_add(lsb_context_t h, int level, int npoly, const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_out,
+            int batch, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        const size_t w = e.c.ct_words(level, npoly);
+        op_add(e, level, npoly, dense(d_a, w), dense(d_b, w), dense(d_out, w), batch);
+    });
+}
+int lsb_sub(lsb_context_t h, int level, int npoly, const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_out,
+            int batch, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        const size_t w = e.c.ct_words(level, npoly);
+        op_sub(e, level, npoly, dense(d_a, w), dense(d_b, w), dense(d_out, w), batch);
+    });
+}
+int lsb_neg(lsb_context_t h, int level, int npoly, const uint64_t* d_a, uint64_t* d_out, int batch, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        const size_t w = e.c.ct_words(level, npoly);
+        op_neg(e, level, npoly, dense(d_a, w), dense(d_out, w), batch);
+    });
+}
+int lsb_add_plain(lsb_context_t h, int level, int npoly, const uint64_t* d_ct, const uint64_t* d_pt,
+                  uint64_t* d_out, int subtract, int batch, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        const size_t w = e.c.ct_words(level, npoly);
+        op_add_plain(e, level, npoly, dense(d_ct, w), dense(d_pt, e.c.ct_words(level, 1)), dense(d_out, w),
+                     subtract != 0, batch);
+    });
+}
+int lsb_add_plain_ringt(lsb_context_t h, int level, int npoly, const uint64_t* d_ct, const uint64_t* d_pt,
+                        uint64_t* d_out, int subtract, int batch, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        const size_t w = e.c.ct_words(level, npoly);
+        op_add_plain_ringt(e, level, npoly, dense(d_ct, w), dense(d_pt, e.c.N), dense(d_out, w), subtract != 0,
+                           batch);
+    });
+}
+int lsb_mul_plain(lsb_context_t h, int level, int npoly, const uint64_t* d_ct, const uint64_t* d_pt,
+                  uint64_t* d_out, int batch, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        const size_t w = e.c.ct_words(level, npoly);
+        op_mul_plain(e, level, npoly, dense(d_ct, w), dense(d_pt, e.c.ct_words(level, 1)), dense(d_out, w), batch);
+    });
+}
+int lsb_mul_plain_ringt(lsb_context_t h, int level, int npoly, const uint64_t* d_ct, const uint64_t* d_pt,
+                        uint64_t* d_out, int batch, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        const size_t w = e.c.ct_words(level, npoly);
+        op_mul_plain_ringt(e, level, npoly, dense(d_ct, w), dense(d_pt, e.c.N), dense(d_out, w), batch);
+    });
+}
+int lsb_mult_relin(lsb_context_t h, int level, const uint64_t* d_a, const uint64_t* d_b, const uint64_t* d_rlk,
+                   int key_level, uint64_t* d_out2, int batch, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        const size_t w = e.c.ct_words(level, 2);
+        op_mult_relin(e, level, dense(d_a, w), dense(d_b, w), d_rlk, key_level, dense(d_out2, w), batch);
+    });
+}
+int lsb_mult_relin_rescale(lsb_context_t h, int level, const uint64_t* d_a, const uint64_t* d_b,
+                           const uint64_t* d_rlk, int key_level, uint64_t* d_out2, int batch, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        const size_t w = e.c.ct_words(level, 2);
+        op_mult_relin_rescale(e, level, dense(d_a, w), dense(d_b, w), d_rlk, key_level,
+                              dense(d_out2, e.c.ct_words(level - 1, 2)), batch);
+    });
+}
+
+}  // extern "C"

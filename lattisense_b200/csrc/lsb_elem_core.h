@@ -1,0 +1,48 @@
+// Per-coefficient bodies of the basis-conversion kernels, LSB_HD so tests/emul can run them on the
+// CPU against the oracle.  Algorithm: Lattigo v4 ring/basis_extension.go (modUpExact /
+// reconstructRNS with a float64 overflow count), restated in oracle/orc_core.hpp:139-202.
+#pragma once
+#include "lsb_kernels.h"
+
+namespace lsb {
+
+// x[i]: source residues of one coefficient.  Writes job.nt outputs through `store(t, value)`;
+// `other(t)` supplies the extra operand of BEX_OTHER_SUB.
+template <class Other, class Store>
+LSB_HD void bex_coeff(const BexJob& job, const ModConst* mods, const u64* x, Other&& other, Store&& store) {
+    if (job.centered) {
+        const u64 s = mods[job.src_mod[0]].q;
+        u64 c = x[0];
+        const bool neg = c >= (s >> 1);
+        if (neg) c = s - c;
+        for (int t = 0; t < job.nt; t++) {
+            const ModConst& m = mods[job.dst_mod[t]];
+            u64 r = barrett64(c, m.bq);
+            store(t, neg ? negmod(r, m.q) : r);
+        }
+        return;
+    }
+    u64 y[kBexMaxSrc];
+    double vf = 0.0;
+    for (int i = 0; i < job.ns; i++) {
+        y[i] = mul_shoup(x[i], job.qhat_inv[i], mods[job.src_mod[i]].q);
+        vf += (double)y[i] / job.s_f64[i];
+    }
+    const int v = (int)(u64)vf;
+    for (int t = 0; t < job.nt; t++) {
+        const ModConst& m = mods[job.dst_mod[t]];
+        Acc128 acc{0, 0};
+        for (int i = 0; i < job.ns; i++) acc_mad(acc, y[i], job.qhat_mod[t][i]);
+        u64 e = barrett128(acc.lo, acc.hi, m.bq);
+        e = submod(e, job.vS[t][v], m.q);
+        if (job.mode == BEX_OTHER_SUB) {
+            u64 d = submod(other(t), e, m.q);
+            e = addmod(mul_shoup(d, job.mulc[t], m.q), job.addc[t], m.q);
+        } else if (job.mode == BEX_SUB_MUL) {
+            e = mul_shoup(submod(e, job.addc[t], m.q), job.mulc[t], m.q);
+        }
+        store(t, e);
+    }
+}
+
+}  // namespace lsb

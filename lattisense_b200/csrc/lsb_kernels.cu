@@ -1,0 +1,442 @@
+// Limb-wise and per-coefficient kernels around the NTT: tensor, add/sub/neg, plaintext multiply,
+// basis extension (ModUp / ModDown), key-switch inner product, rescale, automorphisms.
+// All are HBM-streaming kernels: 128-bit coalesced accesses, grid = (coefficient blocks, rows, batch).
+//
+// Reference call sites replaced: mega_ag_runners/gpu/mega_ag_executors_gpu.cu:71-175 (add/sub/neg),
+// :177-227 (multiply), :229-238 (relinearize), :240-248 (rescale), :264-292 (rotations).
+#include "lsb_elem_core.h"
+#include "lsb_ntt_core.h"  // W2
+
+namespace lsb {
+
+constexpr int kElemThreads = 256;
+
+static inline dim3 elem_grid(int N, int rows, int batch) { return dim3((N / 2 + kElemThreads - 1) / kElemThreads, rows, batch); }
+
+__device__ __forceinline__ W2 ld2(const u64* p, int j2) { return reinterpret_cast<const W2*>(p)[j2]; }
+__device__ __forceinline__ void st2(u64* p, int j2, W2 v) { reinterpret_cast<W2*>(p)[j2] = v; }
+
+// ---- add / sub / neg -------------------------------------------------------------------------
+struct BinArgs {
+    BatchPtr a, b, out;
+    int N, b_rows, op;
+    const ModConst* mods;
+    RowMap map;
+};
+__global__ void __launch_bounds__(kElemThreads) k_binary(const __grid_constant__ BinArgs g) {
+    const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j2 >= g.N / 2) return;
+    const int r = blockIdx.y, b = blockIdx.z;
+    const u64 q = g.mods[g.map.mod[r]].q;
+    const u64* pa = g.a.at(b) + (size_t)g.map.in_slot[r] * g.N;
+    u64* po = g.out.at(b) + (size_t)g.map.out_slot[r] * g.N;
+    W2 x = ld2(pa, j2);
+    if (r < g.b_rows) {
+        W2 y = ld2(g.b.at(b) + (size_t)g.map.in_slot[r] * g.N, j2);
+        if (g.op == OP_ADD) {
+            x.a = addmod(x.a, y.a, q);
+            x.b = addmod(x.b, y.b, q);
+        } else {
+            x.a = submod(x.a, y.a, q);
+            x.b = submod(x.b, y.b, q);
+        }
+    }
+    st2(po, j2, x);
+}
+void launch_binary(const DeviceTables& dt, BinOp op, BatchPtr a, BatchPtr b, BatchPtr out, const RowMap& map,
+                   int b_rows, int batch, cudaStream_t s) {
+    if (batch <= 0 || map.n <= 0) return;
+    BinArgs g{a, b, out, dt.N, b_rows, (int)op, dt.mods, map};
+    k_binary<<<elem_grid(dt.N, map.n, batch), kElemThreads, 0, s>>>(g);
+    LSB_CUDA(cudaGetLastError());
+}
+
+struct NegArgs {
+    BatchPtr a, out;
+    int N;
+    const ModConst* mods;
+    RowMap map;
+};
+__global__ void __launch_bounds__(kElemThreads) k_negate(const __grid_constant__ NegArgs g) {
+    const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j2 >= g.N / 2) return;
+    const int r = blockIdx.y, b = blockIdx.z;
+    const u64 q = g.mods[g.map.mod[r]].q;
+    W2 x = ld2(g.a.at(b) + (size_t)g.map.in_slot[r] * g.N, j2);
+    x.a = negmod(x.a, q);
+    x.b = negmod(x.b, q);
+    st2(g.out.at(b) + (size_t)g.map.out_slot[r] * g.N, j2, x);
+}
+void launch_negate(const DeviceTables& dt, BatchPtr a, BatchPtr out, const RowMap& map, int batch, cudaStream_t s) {
+    if (batch <= 0 || map.n <= 0) return;
+    NegArgs g{a, out, dt.N, dt.mods, map};
+    k_negate<<<elem_grid(dt.N, map.n, batch), kElemThreads, 0, s>>>(g);
+    LSB_CUDA(cudaGetLastError());
+}
+
+// ---- tensor ------------------------------------------------------------------------------------
+struct TensorArgs {
+    BatchPtr a, b, out;
+    int N, nl, in_ps, out_ps;
+    const ModConst* mods;
+    uint8_t mod[64];
+};
+__global__ void __launch_bounds__(kElemThreads) k_tensor(const __grid_constant__ TensorArgs g) {
+    const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j2 >= g.N / 2) return;
+    const int i = blockIdx.y, b = blockIdx.z;
+    const BarrettQ bq = g.mods[g.mod[i]].bq;
+    const u64 q = bq.q;
+    const u64* pa = g.a.at(b);
+    const u64* pb = g.b.at(b);
+    u64* po = g.out.at(b);
+    const size_t N = g.N;
+    const W2 a0 = ld2(pa + (size_t)i * N, j2), a1 = ld2(pa + (size_t)(g.in_ps + i) * N, j2);
+    const W2 b0 = ld2(pb + (size_t)i * N, j2), b1 = ld2(pb + (size_t)(g.in_ps + i) * N, j2);
+    W2 c0, c1, c2;
+    c0.a = mulmod(a0.a, b0.a, bq);
+    c0.b = mulmod(a0.b, b0.b, bq);
+    c2.a = mulmod(a1.a, b1.a, bq);
+    c2.b = mulmod(a1.b, b1.b, bq);
+    {
+        Acc128 t{0, 0};
+        acc_mad(t, a0.a, b1.a);
+        acc_mad(t, a1.a, b0.a);
+        c1.a = barrett128(t.lo, t.hi, bq);
+        Acc128 u{0, 0};
+        acc_mad(u, a0.b, b1.b);
+        acc_mad(u, a1.b, b0.b);
+        c1.b = barrett128(u.lo, u.hi, bq);
+    }
+    (void)q;
+    st2(po + (size_t)i * N, j2, c0);
+    st2(po + (size_t)(g.out_ps + i) * N, j2, c1);
+    st2(po + (size_t)(2 * g.out_ps + i) * N, j2, c2);
+}
+void launch_tensor(const DeviceTables& dt, BatchPtr a, BatchPtr b, BatchPtr out, int nl, int a_poly_stride,
+                   int out_poly_stride, const uint8_t* mod_of_limb, int batch, cudaStream_t s) {
+    if (batch <= 0) return;
+    LSB_CHECK(nl <= 64, "tensor: too many limbs");
+    TensorArgs g;
+    g.a = a;
+    g.b = b;
+    g.out = out;
+    g.N = dt.N;
+    g.nl = nl;
+    g.in_ps = a_poly_stride;
+    g.out_ps = out_poly_stride;
+    g.mods = dt.mods;
+    for (int i = 0; i < nl; i++) g.mod[i] = mod_of_limb[i];
+    k_tensor<<<elem_grid(dt.N, nl, batch), kElemThreads, 0, s>>>(g);
+    LSB_CUDA(cudaGetLastError());
+}
+
+// ---- ct x pt -----------------------------------------------------------------------------------
+struct MulPlainArgs {
+    BatchPtr ct, pt, out;
+    int N, npoly, nl, acc;
+    const ModConst* mods;
+};
+__global__ void __launch_bounds__(kElemThreads) k_mul_plain(const __grid_constant__ MulPlainArgs g) {
+    const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j2 >= g.N / 2) return;
+    const int i = blockIdx.y, b = blockIdx.z;
+    const BarrettQ bq = g.mods[i].bq;
+    const W2 p = ld2(g.pt.at(b) + (size_t)i * g.N, j2);
+    for (int pl = 0; pl < g.npoly; pl++) {
+        const size_t off = (size_t)(pl * g.nl + i) * g.N;
+        const W2 c = ld2(g.ct.at(b) + off, j2);
+        W2 o;
+        o.a = mulmod(c.a, p.a, bq);
+        o.b = mulmod(c.b, p.b, bq);
+        if (g.acc) {
+            const W2 prev = ld2(g.out.at(b) + off, j2);
+            o.a = addmod(o.a, prev.a, bq.q);
+            o.b = addmod(o.b, prev.b, bq.q);
+        }
+        st2(g.out.at(b) + off, j2, o);
+    }
+}
+void launch_mul_plain(const DeviceTables& dt, BatchPtr ct, BatchPtr pt, BatchPtr out, int npoly, int nl,
+                      bool accumulate, int batch, cudaStream_t s) {
+    if (batch <= 0) return;
+    MulPlainArgs g{ct, pt, out, dt.N, npoly, nl, accumulate ? 1 : 0, dt.mods};
+    k_mul_plain<<<elem_grid(dt.N, nl, batch), kElemThreads, 0, s>>>(g);
+    LSB_CUDA(cudaGetLastError());
+}
+
+// ---- basis extension -----------------------------------------------------------------------------
+struct BexArgs {
+    const BexJob* jobs;
+    BatchPtr src, dst, other;
+    int N;
+    const ModConst* mods;
+};
+__global__ void __launch_bounds__(kElemThreads) k_basis_extend(const __grid_constant__ BexArgs g) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= g.N) return;
+    const BexJob& job = g.jobs[blockIdx.y];
+    const int b = blockIdx.z;
+    const u64* ps = g.src.at(b);
+    u64* pd = g.dst.at(b);
+    const u64* po = (job.mode == BEX_OTHER_SUB) ? g.other.at(b) : nullptr;
+    const size_t N = g.N;
+    u64 x[kBexMaxSrc];
+#pragma unroll 4
+    for (int i = 0; i < job.ns; i++) x[i] = ps[(size_t)job.src_slot[i] * N + j];
+    bex_coeff(
+        job, g.mods, x, [&](int t) { return po[(size_t)job.other_slot[t] * N + j]; },
+        [&](int t, u64 v) { pd[(size_t)job.dst_slot[t] * N + j] = v; });
+}
+void launch_basis_extend(const DeviceTables& dt, const BexJob* jobs, int njobs, BatchPtr src, BatchPtr dst,
+                         BatchPtr other, int batch, cudaStream_t s) {
+    if (batch <= 0 || njobs <= 0) return;
+    BexArgs g{jobs, src, dst, other, dt.N, dt.mods};
+    dim3 grid((dt.N + kElemThreads - 1) / kElemThreads, njobs, batch);
+    k_basis_extend<<<grid, kElemThreads, 0, s>>>(g);
+    LSB_CUDA(cudaGetLastError());
+}
+
+// ---- (a - b) * c (+ addend) ------------------------------------------------------------------------
+struct FinishArgs {
+    BatchPtr a, b, addend, out;
+    const FinishMap* fm;
+    int N, has_add;
+    const ModConst* mods;
+};
+__global__ void __launch_bounds__(kElemThreads) k_finish(const __grid_constant__ FinishArgs g) {
+    const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j2 >= g.N / 2) return;
+    const int r = blockIdx.y, b = blockIdx.z;
+    const FinishMap& fm = *g.fm;
+    const u64 q = g.mods[fm.mod[r]].q;
+    const Tw c = fm.c[r];
+    const W2 x = ld2(g.a.at(b) + (size_t)fm.a_slot[r] * g.N, j2);
+    const W2 y = ld2(g.b.at(b) + (size_t)fm.b_slot[r] * g.N, j2);
+    W2 o;
+    o.a = mul_shoup(submod(x.a, y.a, q), c, q);
+    o.b = mul_shoup(submod(x.b, y.b, q), c, q);
+    if (g.has_add && fm.add_slot[r] != 0xFF) {
+        const W2 z = ld2(g.addend.at(b) + (size_t)fm.add_slot[r] * g.N, j2);
+        o.a = addmod(o.a, z.a, q);
+        o.b = addmod(o.b, z.b, q);
+    }
+    st2(g.out.at(b) + (size_t)fm.out_slot[r] * g.N, j2, o);
+}
+void launch_finish(const DeviceTables& dt, BatchPtr a, BatchPtr b, BatchPtr addend, bool has_addend, BatchPtr out,
+                   const FinishMap* fm_dev, int nrows, int batch, cudaStream_t s) {
+    if (batch <= 0 || nrows <= 0) return;
+    FinishArgs g{a, b, addend, out, fm_dev, dt.N, has_addend ? 1 : 0, dt.mods};
+    k_finish<<<elem_grid(dt.N, nrows, batch), kElemThreads, 0, s>>>(g);
+    LSB_CUDA(cudaGetLastError());
+}
+
+// ---- key-switch inner product -------------------------------------------------------------------------
+struct KsInnerK {
+    KsInnerArgs a;
+    int N;
+    const ModConst* mods;
+};
+__global__ void __launch_bounds__(kElemThreads) k_ks_inner(const __grid_constant__ KsInnerK g) {
+    const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j2 >= g.N / 2) return;
+    const KsInnerArgs& a = g.a;
+    const int t = blockIdx.y, b = blockIdx.z;
+    const int lk = a.l + a.k, klimbs = a.key_level + 1 + a.k;
+    const int key_limb = t < a.l ? t : a.key_level + 1 + (t - a.l);
+    const BarrettQ bq = g.mods[t < a.l ? t : a.nq + (t - a.l)].bq;
+    const size_t N = g.N;
+    const u64* pext = a.ext.at(b);
+    const u64* pc = a.cntt.at(b) + (size_t)a.cntt_slot0 * N;
+    Acc128 s0a{0, 0}, s0b{0, 0}, s1a{0, 0}, s1b{0, 0};
+    for (int d = 0; d < a.beta; d++) {
+        const bool own = t < a.l && t >= d * a.alpha && t < (d + 1) * a.alpha;
+        const W2 x = own ? ld2(pc + (size_t)t * N, j2) : ld2(pext + (size_t)(d * lk + t) * N, j2);
+        const W2 e0 = ld2(a.evk + ((size_t)(d * 2 + 0) * klimbs + key_limb) * N, j2);
+        const W2 e1 = ld2(a.evk + ((size_t)(d * 2 + 1) * klimbs + key_limb) * N, j2);
+        acc_mad(s0a, x.a, e0.a);
+        acc_mad(s0b, x.b, e0.b);
+        acc_mad(s1a, x.a, e1.a);
+        acc_mad(s1b, x.b, e1.b);
+    }
+    W2 o0, o1;
+    o0.a = barrett128(s0a.lo, s0a.hi, bq);
+    o0.b = barrett128(s0b.lo, s0b.hi, bq);
+    o1.a = barrett128(s1a.lo, s1a.hi, bq);
+    o1.b = barrett128(s1b.lo, s1b.hi, bq);
+    u64* pacc = a.acc.at(b);
+    st2(pacc + (size_t)t * N, j2, o0);
+    st2(pacc + (size_t)(lk + t) * N, j2, o1);
+}
+void launch_ks_inner(const DeviceTables& dt, const KsInnerArgs& a, int batch, cudaStream_t s) {
+    if (batch <= 0) return;
+    KsInnerK g{a, dt.N, dt.mods};
+    k_ks_inner<<<elem_grid(dt.N, a.l + a.k, batch), kElemThreads, 0, s>>>(g);
+    LSB_CUDA(cudaGetLastError());
+}
+
+// ---- rescale ---------------------------------------------------------------------------------------------
+struct RescaleLiftArgs {
+    BatchPtr last, tmp;
+    int N, npoly, level, last_ps;
+    const ModConst* mods;
+};
+// last: coefficient-domain limb `level` of each polynomial (block [npoly] with stride last_ps limbs)
+__global__ void __launch_bounds__(kElemThreads) k_rescale_lift(const __grid_constant__ RescaleLiftArgs g) {
+    const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j2 >= g.N / 2) return;
+    const int p = blockIdx.y, b = blockIdx.z;
+    const u64 ql = g.mods[g.level].q, half = (ql - 1) >> 1;
+    W2 x = ld2(g.last.at(b) + (size_t)p * g.last_ps * g.N, j2);
+    x.a = addmod(x.a, half, ql);
+    x.b = addmod(x.b, half, ql);
+    u64* pt = g.tmp.at(b) + (size_t)p * g.level * g.N;
+    for (int i = 0; i < g.level; i++) {
+        const ModConst& m = g.mods[i];
+        const u64 hq = barrett64(half, m.bq);
+        W2 o;
+        o.a = submod(barrett64(x.a, m.bq), hq, m.q);
+        o.b = submod(barrett64(x.b, m.bq), hq, m.q);
+        st2(pt + (size_t)i * g.N, j2, o);
+    }
+}
+void launch_rescale_lift(const DeviceTables& dt, BatchPtr last, int last_poly_stride, BatchPtr tmp, int npoly, int level,
+                         int batch, cudaStream_t s) {
+    if (batch <= 0) return;
+    RescaleLiftArgs g{last, tmp, dt.N, npoly, level, last_poly_stride, dt.mods};
+    k_rescale_lift<<<elem_grid(dt.N, npoly, batch), kElemThreads, 0, s>>>(g);
+    LSB_CUDA(cudaGetLastError());
+}
+
+struct BfvRescaleArgs {
+    BatchPtr in, out;
+    int N, npoly, level;
+    const Tw* qlinv;  // [level] (ql^-1 mod q_i)
+    const ModConst* mods;
+};
+__global__ void __launch_bounds__(kElemThreads) k_bfv_rescale(const __grid_constant__ BfvRescaleArgs g) {
+    const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j2 >= g.N / 2) return;
+    const int p = blockIdx.y, b = blockIdx.z;
+    const int l = g.level + 1;
+    const u64 ql = g.mods[g.level].q, half = (ql - 1) >> 1;
+    const u64* pin = g.in.at(b) + (size_t)p * l * g.N;
+    u64* pout = g.out.at(b) + (size_t)p * (l - 1) * g.N;
+    W2 x = ld2(pin + (size_t)g.level * g.N, j2);
+    x.a = addmod(x.a, half, ql);
+    x.b = addmod(x.b, half, ql);
+    for (int i = 0; i < g.level; i++) {
+        const ModConst& m = g.mods[i];
+        const u64 hq = barrett64(half, m.bq);
+        const Tw c = g.qlinv[i];
+        const W2 sv = ld2(pin + (size_t)i * g.N, j2);
+        W2 o;
+        o.a = mul_shoup(submod(sv.a, submod(barrett64(x.a, m.bq), hq, m.q), m.q), c, m.q);
+        o.b = mul_shoup(submod(sv.b, submod(barrett64(x.b, m.bq), hq, m.q), m.q), c, m.q);
+        st2(pout + (size_t)i * g.N, j2, o);
+    }
+}
+void launch_bfv_rescale(const DeviceTables& dt, BatchPtr in, BatchPtr out, int npoly, int level, const Tw* qlinv_dev,
+                        int batch, cudaStream_t s) {
+    if (batch <= 0) return;
+    BfvRescaleArgs g{in, out, dt.N, npoly, level, qlinv_dev, dt.mods};
+    k_bfv_rescale<<<elem_grid(dt.N, npoly, batch), kElemThreads, 0, s>>>(g);
+    LSB_CUDA(cudaGetLastError());
+}
+
+// ---- automorphisms -----------------------------------------------------------------------------------------
+struct PermArgs {
+    BatchPtr in, out;
+    int N, logN;
+    const u32* index;
+    u64 gal;
+    const ModConst* mods;
+    RowMap map;
+};
+__global__ void __launch_bounds__(kElemThreads) k_permute_ntt(const __grid_constant__ PermArgs g) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= g.N) return;
+    const int r = blockIdx.y, b = blockIdx.z;
+    const u64* pi = g.in.at(b) + (size_t)g.map.in_slot[r] * g.N;
+    u64* po = g.out.at(b) + (size_t)g.map.out_slot[r] * g.N;
+    po[j] = pi[g.index[j]];
+}
+void launch_permute_ntt(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap& map, const u32* index,
+                        int batch, cudaStream_t s) {
+    if (batch <= 0 || map.n <= 0) return;
+    PermArgs g{in, out, dt.N, dt.logN, index, 0, dt.mods, map};
+    dim3 grid((dt.N + kElemThreads - 1) / kElemThreads, map.n, batch);
+    k_permute_ntt<<<grid, kElemThreads, 0, s>>>(g);
+    LSB_CUDA(cudaGetLastError());
+}
+// ring.Permute: X^i -> X^(i*gal); scatter form out[(i*gal) mod N] = +-in[i]
+__global__ void __launch_bounds__(kElemThreads) k_permute_coeff(const __grid_constant__ PermArgs g) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= g.N) return;
+    const int r = blockIdx.y, b = blockIdx.z;
+    const u64 q = g.mods[g.map.mod[r]].q;
+    const u64* pi = g.in.at(b) + (size_t)g.map.in_slot[r] * g.N;
+    u64* po = g.out.at(b) + (size_t)g.map.out_slot[r] * g.N;
+    const u64 idx = (u64)j * g.gal;
+    const u64 v = pi[j];
+    po[idx & (u64)(g.N - 1)] = ((idx >> g.logN) & 1) ? negmod(v, q) : v;
+}
+void launch_permute_coeff(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap& map, u64 gal, int batch,
+                          cudaStream_t s) {
+    if (batch <= 0 || map.n <= 0) return;
+    PermArgs g{in, out, dt.N, dt.logN, nullptr, gal, dt.mods, map};
+    dim3 grid((dt.N + kElemThreads - 1) / kElemThreads, map.n, batch);
+    k_permute_coeff<<<grid, kElemThreads, 0, s>>>(g);
+    LSB_CUDA(cudaGetLastError());
+}
+
+// ---- plaintext helpers -----------------------------------------------------------------------------------------
+struct LiftArgs {
+    BatchPtr in, out;
+    int N, nl;
+};
+__global__ void __launch_bounds__(kElemThreads) k_lift_ringt(const __grid_constant__ LiftArgs g) {
+    const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j2 >= g.N / 2) return;
+    const int b = blockIdx.z;
+    const W2 x = ld2(g.in.at(b), j2);
+    u64* po = g.out.at(b);
+    for (int i = 0; i < g.nl; i++) st2(po + (size_t)i * g.N, j2, x);
+}
+void launch_lift_ringt(const DeviceTables& dt, BatchPtr in, BatchPtr out, int nl, int batch, cudaStream_t s) {
+    if (batch <= 0) return;
+    LiftArgs g{in, out, dt.N, nl};
+    k_lift_ringt<<<elem_grid(dt.N, 1, batch), kElemThreads, 0, s>>>(g);
+    LSB_CUDA(cudaGetLastError());
+}
+
+struct ScaleUpArgs {
+    BatchPtr in, out;
+    int N, nl;
+    const ScaleUpConsts* sc;
+    const ModConst* mods;
+};
+__global__ void __launch_bounds__(kElemThreads) k_bfv_scale_up(const __grid_constant__ ScaleUpArgs g) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= g.N) return;
+    const int b = blockIdx.z;
+    const ScaleUpConsts& sc = *g.sc;
+    const u64 m = barrett64(g.in.at(b)[j], sc.bt);
+    const u64 r = addmod(mulmod(m, sc.qmodt, sc.bt), sc.thalf, sc.t);
+    u64* po = g.out.at(b);
+    for (int i = 0; i < g.nl; i++) {
+        const ModConst& mc = g.mods[i];
+        const u64 v = submod(barrett64(r, mc.bq), sc.thalf_q[i], mc.q);
+        po[(size_t)i * g.N + j] = mul_shoup(v, sc.neg_tinv[i], mc.q);
+    }
+}
+void launch_bfv_scale_up(const DeviceTables& dt, BatchPtr in, BatchPtr out, int nl, const ScaleUpConsts* sc_dev,
+                         int batch, cudaStream_t s) {
+    if (batch <= 0) return;
+    ScaleUpArgs g{in, out, dt.N, nl, sc_dev, dt.mods};
+    dim3 grid((dt.N + kElemThreads - 1) / kElemThreads, 1, batch);
+    k_bfv_scale_up<<<grid, kElemThreads, 0, s>>>(g);
+    LSB_CUDA(cudaGetLastError());
+}
+
+}  // namespace lsb

@@ -1,0 +1,103 @@
+// Kernel launchers of the B200 executor core (all asynchronous on the given stream).
+#pragma once
+#include "lsb_common.h"
+
+namespace lsb {
+
+// Device-resident tables of one context (one parameter set on one GPU).
+struct DeviceTables {
+    int device = 0;
+    int sm_count = 148;
+    int logN = 0, N = 0;
+    int nmod = 0;
+    const Tw* tw_fwd = nullptr;  // [nmod][N]  psi^bitrev(i) with Shoup companion
+    const Tw* tw_inv = nullptr;  // [nmod][N]  psi^-bitrev(i)
+    const ModConst* mods = nullptr;
+};
+
+// ---- NTT ----
+void launch_ntt(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap& map, int batch, bool inverse,
+                cudaStream_t s);
+
+// ---- basis extension (ModUp / ModDown / BFV scaling), Lattigo-style with float64 overflow count ----
+constexpr int kBexMaxSrc = 16;
+constexpr int kBexMaxDst = 48;
+enum BexMode {
+    BEX_PLAIN = 0,      // dst = ext
+    BEX_OTHER_SUB = 1,  // dst = (other - ext) * mulc + addc
+    BEX_SUB_MUL = 2,    // dst = (ext - addc) * mulc
+};
+struct BexJob {
+    int ns, nt, mode;
+    int centered;  // ns == 1 in key-switch ModUp: centred lift instead of the CRT formula
+    uint8_t src_slot[kBexMaxSrc], src_mod[kBexMaxSrc];
+    uint8_t dst_slot[kBexMaxDst], dst_mod[kBexMaxDst], other_slot[kBexMaxDst];
+    Tw qhat_inv[kBexMaxSrc];
+    double s_f64[kBexMaxSrc];
+    u64 qhat_mod[kBexMaxDst][kBexMaxSrc];
+    u64 vS[kBexMaxDst][kBexMaxSrc + 1];
+    Tw mulc[kBexMaxDst];
+    u64 addc[kBexMaxDst];
+};
+// jobs: device array of njobs BexJob; src/dst/other: per-batch-item blocks.
+void launch_basis_extend(const DeviceTables& dt, const BexJob* jobs, int njobs, BatchPtr src, BatchPtr dst,
+                         BatchPtr other, int batch, cudaStream_t s);
+
+// ---- limb-wise kernels ----
+enum BinOp { OP_ADD = 0, OP_SUB = 1 };
+// out[r] = a[r] (op) b[r] for r < map.n ; rows r >= b_rows copy a (or negate-free pass through)
+void launch_binary(const DeviceTables& dt, BinOp op, BatchPtr a, BatchPtr b, BatchPtr out, const RowMap& map,
+                   int b_rows, int batch, cudaStream_t s);
+void launch_negate(const DeviceTables& dt, BatchPtr a, BatchPtr out, const RowMap& map, int batch, cudaStream_t s);
+// degree-1 x degree-1 tensor over nl limbs: a,b blocks [2][a_stride_limbs] -> out [3][nl]
+void launch_tensor(const DeviceTables& dt, BatchPtr a, BatchPtr b, BatchPtr out, int nl, int a_poly_stride,
+                   int out_poly_stride, const uint8_t* mod_of_limb, int batch, cudaStream_t s);
+// out[p][i] (+)= ct[p][i] * pt[i]  (NTT domain), p < npoly
+void launch_mul_plain(const DeviceTables& dt, BatchPtr ct, BatchPtr pt, BatchPtr out, int npoly, int nl,
+                      bool accumulate, int batch, cudaStream_t s);
+// out[r] = (a[a_slot[r]] - b[b_slot[r]]) * c_r (+ addend[add_slot[r]])   (ModDown / rescale finish)
+struct FinishMap {
+    int n;
+    uint8_t a_slot[kMaxRows], b_slot[kMaxRows], add_slot[kMaxRows], out_slot[kMaxRows], mod[kMaxRows];
+    Tw c[kMaxRows];  // multiplier of row r (Shoup pair w.r.t. the row's modulus)
+};
+void launch_finish(const DeviceTables& dt, BatchPtr a, BatchPtr b, BatchPtr addend, bool has_addend, BatchPtr out,
+                   const FinishMap* fm_dev, int nrows, int batch, cudaStream_t s);
+
+// key-switch inner product: acc[p][t] = sum_d D_d[t] * evk[d][p][keylimb(t)]
+struct KsInnerArgs {
+    BatchPtr ext;    // [beta][l+k] limbs (own-digit slots unused)
+    BatchPtr cntt;   // NTT-domain input polynomial
+    int cntt_slot0;  // limb t of the input polynomial is at slot cntt_slot0 + t
+    const u64* evk;  // [beta_key][2][key_level+1+k][N]
+    BatchPtr acc;    // [2][l+k]
+    int l, k, beta, alpha, key_level;
+    int nq;  // modulus index of P_0
+};
+void launch_ks_inner(const DeviceTables& dt, const KsInnerArgs& a, int batch, cudaStream_t s);
+
+// CKKS rescale lift: tmp[p][i] = ((last[p] + half) mod q_i) - half mod q_i, i < level
+void launch_rescale_lift(const DeviceTables& dt, BatchPtr last, int last_poly_stride, BatchPtr tmp, int npoly, int level,
+                         int batch, cudaStream_t s);
+// BFV rescale (coefficient domain, fully fused): [np][l] -> [np][l-1]
+void launch_bfv_rescale(const DeviceTables& dt, BatchPtr in, BatchPtr out, int npoly, int level, const Tw* qlinv_dev,
+                        int batch, cudaStream_t s);
+
+// automorphisms over rows of map: NTT domain gather (index table) / coefficient domain signed permutation
+void launch_permute_ntt(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap& map, const u32* index,
+                        int batch, cudaStream_t s);
+void launch_permute_coeff(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap& map, u64 gal, int batch,
+                          cudaStream_t s);
+// lift a single-limb plaintext mod t (pt_ringt) onto nl limbs (values in [0,t) are copied as they are)
+void launch_lift_ringt(const DeviceTables& dt, BatchPtr in, BatchPtr out, int nl, int batch, cudaStream_t s);
+// BFV ScaleUp of a mod-t plaintext: out_i = round(Q*m/t) mod q_i
+struct ScaleUpConsts {
+    u64 t, thalf, qmodt;
+    BarrettQ bt;
+    u64 thalf_q[64];
+    Tw neg_tinv[64];
+};
+void launch_bfv_scale_up(const DeviceTables& dt, BatchPtr in, BatchPtr out, int nl, const ScaleUpConsts* sc_dev,
+                         int batch, cudaStream_t s);
+
+}  // namespace lsb

@@ -1,0 +1,484 @@
+// Ciphertext-level operations: host orchestration of the kernel pipeline (no arithmetic here).
+//
+// Hybrid key-switch (relinearize / rotate) per batch chunk, l = level+1, k = |P|, beta = ceil(l/k):
+//   [INTT c] -> ModUp (beta digits, Lattigo float-v CRT) -> NTT of the extended limbs ->
+//   inner product with the evaluation key -> INTT of the 2k P-limbs -> ModDown extension ->
+//   NTT -> (acc - ext) * P^-1 (+ c0/c1).
+// Scratch for a chunk is sized to stay L2-resident (126 MB) so that only the ciphertexts and the
+// evaluation key are streamed from HBM.
+#include <cstdlib>
+#include <algorithm>
+#include "lsb_ops.h"
+
+namespace lsb {
+
+static BatchPtr adv(BatchPtr p, int b0) {
+    if (p.table) p.table += b0;
+    else p.base += (size_t)b0 * p.stride;
+    return p;
+}
+
+static size_t scratch_budget_words() {
+    static size_t v = [] {
+        const char* e = getenv("LSB_SCRATCH_MB");
+        size_t mb = e ? (size_t)atol(e) : 96;
+        if (mb < 8) mb = 8;
+        return mb * (1u << 20) / 8;
+    }();
+    return v;
+}
+
+// Largest chunk within the scratch budget whose dominant NTT launch fills whole waves of SMs.
+static int pick_chunk(const OpEnv& e, size_t item_words, int batch, int rows_per_item) {
+    if (e.chunk > 0) return std::min(e.chunk, batch);
+    int cmax = (int)std::max<size_t>(1, scratch_budget_words() / std::max<size_t>(item_words, 1));
+    if (cmax >= batch) return batch;
+    if (e.c.logN > 14 || rows_per_item <= 0) return cmax;
+    const int sms = e.c.dt.sm_count;
+    int best = cmax;
+    double best_eff = 0;
+    for (int c = cmax; c >= std::max(1, cmax / 2); c--) {
+        const int rows = c * rows_per_item;
+        const double eff = (double)rows / (double)(((rows + sms - 1) / sms) * sms);
+        if (eff > best_eff + 1e-9) {
+            best_eff = eff;
+            best = c;
+        }
+    }
+    return best;
+}
+
+static RowMap rowmap_seq(int n, int in0, int out0, int mod0, int period) {
+    LSB_CHECK(n <= kMaxRows, "lsb: too many rows in one launch");
+    RowMap m;
+    m.n = n;
+    for (int r = 0; r < n; r++) {
+        m.in_slot[r] = (uint8_t)(in0 + r);
+        m.out_slot[r] = (uint8_t)(out0 + r);
+        m.mod[r] = (uint8_t)(mod0 + (period ? r % period : r));
+    }
+    return m;
+}
+
+// ---------------------------------------------------------------------------------------------
+// key-switch core
+// ---------------------------------------------------------------------------------------------
+static int ks_scratch_limbs(const Context& c, int level) {
+    const int l = level + 1, lk = l + c.np;
+    return c.beta(level) * lk + 2 * lk + 2 * l;
+}
+
+// res[p*res_ps + i] = (acc_p[i] - md_p[i]) * P^-1 (+ addend[p*l + i] if addmask bit p), NTT domain
+static void ks_core(OpEnv& e, int level, BatchPtr c_coeff, int coeff_slot0, BatchPtr c_ntt, int ntt_slot0,
+                    const u64* evk, int key_level, BatchPtr addend, int addmask, BatchPtr res, int res_ps,
+                    u64* scratch, size_t item_words, int nb) {
+    Context& c = e.c;
+    const DeviceTables& dt = c.dt;
+    const int l = level + 1, k = c.np, lk = l + k, beta = c.beta(level), alpha = k;
+    const size_t N = c.N;
+    LSB_CHECK(key_level >= level, "lsb: evaluation key level below ciphertext level");
+    BatchPtr ext = bp_strided(scratch, item_words);
+    BatchPtr acc = bp_strided(scratch + (size_t)beta * lk * N, item_words);
+    BatchPtr md = bp_strided(scratch + (size_t)(beta * lk + 2 * lk) * N, item_words);
+
+    launch_basis_extend(dt, c.modup_jobs(level, coeff_slot0), beta, c_coeff, ext, ext, nb, e.s);
+    {
+        RowMap m;
+        m.n = 0;
+        for (int d = 0; d < beta; d++)
+            for (int t = 0; t < lk; t++) {
+                if (t < l && t >= d * alpha && t < (d + 1) * alpha) continue;
+                LSB_CHECK(m.n < kMaxRows, "lsb: too many extended limbs");
+                m.in_slot[m.n] = m.out_slot[m.n] = (uint8_t)(d * lk + t);
+                m.mod[m.n] = (uint8_t)(t < l ? t : c.idxP(t - l));
+                m.n++;
+            }
+        launch_ntt(dt, ext, ext, m, nb, false, e.s);
+    }
+    KsInnerArgs ia;
+    ia.ext = ext;
+    ia.cntt = c_ntt;
+    ia.cntt_slot0 = ntt_slot0;
+    ia.evk = evk;
+    ia.acc = acc;
+    ia.l = l;
+    ia.k = k;
+    ia.beta = beta;
+    ia.alpha = alpha;
+    ia.key_level = key_level;
+    ia.nq = c.nq;
+    launch_ks_inner(dt, ia, nb, e.s);
+    {
+        RowMap m;
+        m.n = 0;
+        for (int p = 0; p < 2; p++)
+            for (int j = 0; j < k; j++) {
+                m.in_slot[m.n] = m.out_slot[m.n] = (uint8_t)(p * lk + l + j);
+                m.mod[m.n] = (uint8_t)c.idxP(j);
+                m.n++;
+            }
+        launch_ntt(dt, acc, acc, m, nb, true, e.s);
+    }
+    launch_basis_extend(dt, c.moddown_jobs(level), 2, acc, md, md, nb, e.s);
+    launch_ntt(dt, md, md, rowmap_seq(2 * l, 0, 0, 0, l), nb, false, e.s);
+    launch_finish(dt, acc, md, addend, addmask != 0, res, c.moddown_finish(level, addmask, res_ps), 2 * l, nb, e.s);
+}
+
+// ---------------------------------------------------------------------------------------------
+// mult
+// ---------------------------------------------------------------------------------------------
+static void ckks_tensor(OpEnv& e, int level, BatchPtr a, BatchPtr b, BatchPtr out3, int nb) {
+    const int l = level + 1;
+    uint8_t mods[64];
+    LSB_CHECK(l <= 64, "lsb: too many limbs");
+    for (int i = 0; i < l; i++) mods[i] = (uint8_t)i;
+    launch_tensor(e.c.dt, a, b, out3, l, l, l, mods, nb, e.s);
+}
+
+static int bfv_mult_scratch_limbs(const Context& c, int level) {
+    const int l = level + 1, lm = c.level_qmul[level] + 1, L = l + lm;
+    return 2 * L + 2 * L + 3 * L + 3 * lm;
+}
+// bfv evaluator tensorAndRescale (oracle/orc_core.hpp:420-484)
+static void bfv_mult_impl(OpEnv& e, int level, BatchPtr a, BatchPtr b, BatchPtr out3, u64* scratch, size_t item_words,
+                          int nb) {
+    Context& c = e.c;
+    const DeviceTables& dt = c.dt;
+    const int l = level + 1, lm = c.level_qmul[level] + 1, L = l + lm;
+    const size_t N = c.N;
+    BatchPtr ea = bp_strided(scratch, item_words);
+    BatchPtr eb = bp_strided(scratch + (size_t)2 * L * N, item_words);
+    BatchPtr prod = bp_strided(scratch + (size_t)4 * L * N, item_words);
+    BatchPtr buf = bp_strided(scratch + (size_t)7 * L * N, item_words);
+    const BexJob* up = c.bfv_q_to_qmul_jobs(level);
+    RowMap mq, mm;  // Q limbs: input -> extended block ; QMul limbs: in place
+    mq.n = mm.n = 0;
+    for (int p = 0; p < 2; p++) {
+        for (int i = 0; i < l; i++) {
+            mq.in_slot[mq.n] = (uint8_t)(p * l + i);
+            mq.out_slot[mq.n] = (uint8_t)(p * L + i);
+            mq.mod[mq.n++] = (uint8_t)i;
+        }
+        for (int j = 0; j < lm; j++) {
+            mm.in_slot[mm.n] = mm.out_slot[mm.n] = (uint8_t)(p * L + l + j);
+            mm.mod[mm.n++] = (uint8_t)c.idxQM(j);
+        }
+    }
+    const BatchPtr ins[2] = {a, b};
+    const BatchPtr exts[2] = {ea, eb};
+    for (int w = 0; w < 2; w++) {
+        launch_basis_extend(dt, up, 2, ins[w], exts[w], exts[w], nb, e.s);
+        launch_ntt(dt, ins[w], exts[w], mq, nb, false, e.s);
+        launch_ntt(dt, exts[w], exts[w], mm, nb, false, e.s);
+    }
+    uint8_t mods[64];
+    LSB_CHECK(L <= 64, "lsb: too many limbs");
+    for (int i = 0; i < l; i++) mods[i] = (uint8_t)i;
+    for (int j = 0; j < lm; j++) mods[l + j] = (uint8_t)c.idxQM(j);
+    launch_tensor(dt, ea, eb, prod, L, L, L, mods, nb, e.s);
+    {
+        RowMap m;
+        m.n = 3 * L;
+        LSB_CHECK(m.n <= kMaxRows, "lsb: too many limbs");
+        for (int r = 0; r < 3 * L; r++) {
+            m.in_slot[r] = m.out_slot[r] = (uint8_t)r;
+            m.mod[r] = mods[r % L];
+        }
+        launch_ntt(dt, prod, prod, m, nb, true, e.s);
+    }
+    launch_basis_extend(dt, c.bfv_quant1_jobs(level), 3, prod, buf, prod, nb, e.s);
+    launch_basis_extend(dt, c.bfv_quant2_jobs(level), 3, buf, out3, buf, nb, e.s);
+}
+
+void op_mult(OpEnv& e, int level, BatchPtr a, BatchPtr b, BatchPtr out3, int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    if (e.c.scheme == SCHEME_CKKS) {
+        ckks_tensor(e, level, a, b, out3, batch);
+        return;
+    }
+    const size_t item = (size_t)bfv_mult_scratch_limbs(e.c, level) * e.c.N;
+    const int l = level + 1, L = l + e.c.level_qmul[level] + 1;
+    const int chunk = pick_chunk(e, item, batch, 3 * L);
+    u64* scratch = e.ws.reserve(item * chunk, e.s);
+    for (int b0 = 0; b0 < batch; b0 += chunk) {
+        const int nb = std::min(chunk, batch - b0);
+        bfv_mult_impl(e, level, adv(a, b0), adv(b, b0), adv(out3, b0), scratch, item, nb);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// relinearize
+// ---------------------------------------------------------------------------------------------
+static int relin_scratch_limbs(const Context& c, int level) {
+    const int l = level + 1;
+    return (c.scheme == SCHEME_CKKS ? l : 3 * l) + ks_scratch_limbs(c, level);
+}
+static void relin_impl(OpEnv& e, int level, BatchPtr ct3, const u64* rlk, int key_level, BatchPtr out2, u64* scratch,
+                       size_t item_words, int nb) {
+    Context& c = e.c;
+    const DeviceTables& dt = c.dt;
+    const int l = level + 1;
+    const size_t N = c.N;
+    if (c.scheme == SCHEME_CKKS) {
+        BatchPtr c2 = bp_strided(scratch, item_words);
+        launch_ntt(dt, ct3, c2, rowmap_seq(l, 2 * l, 0, 0, l), nb, true, e.s);
+        ks_core(e, level, c2, 0, ct3, 2 * l, rlk, key_level, ct3, 3, out2, l, scratch + (size_t)l * N, item_words, nb);
+    } else {
+        // coefficient-domain ciphertext: c2 itself feeds ModUp, NTT(c2) feeds the own-digit products
+        BatchPtr cn = bp_strided(scratch, item_words);
+        BatchPtr tmp = bp_strided(scratch + (size_t)l * N, item_words);
+        launch_ntt(dt, ct3, cn, rowmap_seq(l, 2 * l, 0, 0, l), nb, false, e.s);
+        ks_core(e, level, ct3, 2 * l, cn, 0, rlk, key_level, tmp, 0, tmp, l, scratch + (size_t)3 * l * N, item_words,
+                nb);
+        launch_ntt(dt, tmp, tmp, rowmap_seq(2 * l, 0, 0, 0, l), nb, true, e.s);
+        launch_binary(dt, OP_ADD, tmp, ct3, out2, rowmap_seq(2 * l, 0, 0, 0, l), 2 * l, nb, e.s);
+    }
+}
+void op_relin(OpEnv& e, int level, BatchPtr ct3, const u64* rlk, int key_level, BatchPtr out2, int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    const size_t item = (size_t)relin_scratch_limbs(e.c, level) * e.c.N;
+    const int l = level + 1;
+    const int chunk = pick_chunk(e, item, batch, e.c.beta(level) * (l + e.c.np) - l);
+    u64* scratch = e.ws.reserve(item * chunk, e.s);
+    for (int b0 = 0; b0 < batch; b0 += chunk) {
+        const int nb = std::min(chunk, batch - b0);
+        relin_impl(e, level, adv(ct3, b0), rlk, key_level, adv(out2, b0), scratch, item, nb);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// rescale / drop level
+// ---------------------------------------------------------------------------------------------
+static int rescale_scratch_limbs(const Context& c, int level, int npoly) {
+    return c.scheme == SCHEME_CKKS ? npoly * (1 + level) : 0;
+}
+static void rescale_impl(OpEnv& e, int level, int npoly, BatchPtr in, BatchPtr out, u64* scratch, size_t item_words,
+                         int nb) {
+    Context& c = e.c;
+    const DeviceTables& dt = c.dt;
+    const int l = level + 1;
+    const size_t N = c.N;
+    LSB_CHECK(level >= 1, "lsb: cannot rescale a level-0 ciphertext");
+    if (c.scheme == SCHEME_BFV) {
+        launch_bfv_rescale(dt, in, out, npoly, level, c.qlinv(level), nb, e.s);
+        return;
+    }
+    // ring.DivRoundByLastModulusNTT
+    BatchPtr last = bp_strided(scratch, item_words);
+    BatchPtr tmp = bp_strided(scratch + (size_t)npoly * N, item_words);
+    RowMap m;
+    m.n = npoly;
+    for (int p = 0; p < npoly; p++) {
+        m.in_slot[p] = (uint8_t)(p * l + level);
+        m.out_slot[p] = (uint8_t)p;
+        m.mod[p] = (uint8_t)level;
+    }
+    launch_ntt(dt, in, last, m, nb, true, e.s);
+    launch_rescale_lift(dt, last, 1, tmp, npoly, level, nb, e.s);
+    launch_ntt(dt, tmp, tmp, rowmap_seq(npoly * level, 0, 0, 0, level), nb, false, e.s);
+    launch_finish(dt, in, tmp, tmp, false, out, c.rescale_finish(level, npoly), npoly * level, nb, e.s);
+}
+void op_rescale(OpEnv& e, int level, int npoly, BatchPtr in, BatchPtr out, int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    const size_t item = (size_t)rescale_scratch_limbs(e.c, level, npoly) * e.c.N;
+    const int chunk = item ? pick_chunk(e, item, batch, npoly * level) : batch;
+    u64* scratch = item ? e.ws.reserve(item * chunk, e.s) : nullptr;
+    for (int b0 = 0; b0 < batch; b0 += chunk) {
+        const int nb = std::min(chunk, batch - b0);
+        rescale_impl(e, level, npoly, adv(in, b0), adv(out, b0), scratch, item, nb);
+    }
+}
+
+void op_drop_level(OpEnv& e, int level, int npoly, BatchPtr in, BatchPtr out, int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    LSB_CHECK(level >= 1, "lsb: cannot drop below level 0");
+    const int l = level + 1;
+    RowMap m;
+    m.n = npoly * (l - 1);
+    LSB_CHECK(m.n <= kMaxRows, "lsb: too many limbs");
+    for (int p = 0; p < npoly; p++)
+        for (int i = 0; i < l - 1; i++) {
+            const int r = p * (l - 1) + i;
+            m.in_slot[r] = (uint8_t)(p * l + i);
+            m.out_slot[r] = (uint8_t)r;
+            m.mod[r] = (uint8_t)i;
+        }
+    // copy through the binary kernel with no second operand rows
+    launch_binary(e.c.dt, OP_ADD, in, in, out, m, 0, batch, e.s);
+}
+
+// ---------------------------------------------------------------------------------------------
+// rotate (automorphism + key-switch)
+// ---------------------------------------------------------------------------------------------
+static int rotate_scratch_limbs(const Context& c, int level) { return 3 * (level + 1) + ks_scratch_limbs(c, level); }
+static void rotate_impl(OpEnv& e, int level, BatchPtr ct, const u64* glk, int key_level, u64 gal, BatchPtr out,
+                        u64* scratch, size_t item_words, int nb) {
+    Context& c = e.c;
+    const DeviceTables& dt = c.dt;
+    const int l = level + 1;
+    const size_t N = c.N;
+    BatchPtr c1x = bp_strided(scratch, item_words);                   // c1 in the other domain
+    BatchPtr tmp = bp_strided(scratch + (size_t)l * N, item_words);   // [2][l]
+    u64* ks_scratch = scratch + (size_t)3 * l * N;
+    if (c.scheme == SCHEME_CKKS) {
+        // ckks evaluator permuteNTT: key-switch c1, add c0, permute both (oracle/orc_core.hpp:402-414)
+        launch_ntt(dt, ct, c1x, rowmap_seq(l, l, 0, 0, l), nb, true, e.s);
+        ks_core(e, level, c1x, 0, ct, l, glk, key_level, ct, 1, tmp, l, ks_scratch, item_words, nb);
+        launch_permute_ntt(dt, tmp, out, rowmap_seq(2 * l, 0, 0, 0, l), c.permute_index(gal), nb, e.s);
+    } else {
+        launch_ntt(dt, ct, c1x, rowmap_seq(l, l, 0, 0, l), nb, false, e.s);
+        ks_core(e, level, ct, l, c1x, 0, glk, key_level, tmp, 0, tmp, l, ks_scratch, item_words, nb);
+        launch_ntt(dt, tmp, tmp, rowmap_seq(2 * l, 0, 0, 0, l), nb, true, e.s);
+        launch_binary(dt, OP_ADD, tmp, ct, tmp, rowmap_seq(2 * l, 0, 0, 0, l), l, nb, e.s);
+        launch_permute_coeff(dt, tmp, out, rowmap_seq(2 * l, 0, 0, 0, l), gal, nb, e.s);
+    }
+}
+void op_rotate(OpEnv& e, int level, BatchPtr ct, const u64* glk, int key_level, u64 gal, BatchPtr out, int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    const size_t item = (size_t)rotate_scratch_limbs(e.c, level) * e.c.N;
+    const int l = level + 1;
+    const int chunk = pick_chunk(e, item, batch, e.c.beta(level) * (l + e.c.np) - l);
+    u64* scratch = e.ws.reserve(item * chunk, e.s);
+    for (int b0 = 0; b0 < batch; b0 += chunk) {
+        const int nb = std::min(chunk, batch - b0);
+        rotate_impl(e, level, adv(ct, b0), glk, key_level, gal, adv(out, b0), scratch, item, nb);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// add / sub / neg and plaintext variants
+// ---------------------------------------------------------------------------------------------
+void op_add(OpEnv& e, int level, int npoly, BatchPtr a, BatchPtr b, BatchPtr out, int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    const int l = level + 1;
+    launch_binary(e.c.dt, OP_ADD, a, b, out, rowmap_seq(npoly * l, 0, 0, 0, l), npoly * l, batch, e.s);
+}
+void op_sub(OpEnv& e, int level, int npoly, BatchPtr a, BatchPtr b, BatchPtr out, int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    const int l = level + 1;
+    launch_binary(e.c.dt, OP_SUB, a, b, out, rowmap_seq(npoly * l, 0, 0, 0, l), npoly * l, batch, e.s);
+}
+void op_neg(OpEnv& e, int level, int npoly, BatchPtr a, BatchPtr out, int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    const int l = level + 1;
+    launch_negate(e.c.dt, a, out, rowmap_seq(npoly * l, 0, 0, 0, l), batch, e.s);
+}
+void op_add_plain(OpEnv& e, int level, int npoly, BatchPtr ct, BatchPtr pt, BatchPtr out, bool subtract, int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    const int l = level + 1;
+    launch_binary(e.c.dt, subtract ? OP_SUB : OP_ADD, ct, pt, out, rowmap_seq(npoly * l, 0, 0, 0, l), l, batch, e.s);
+}
+void op_add_plain_ringt(OpEnv& e, int level, int npoly, BatchPtr ct, BatchPtr pt, BatchPtr out, bool subtract,
+                        int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    Context& c = e.c;
+    const int l = level + 1;
+    const size_t item = (size_t)l * c.N;
+    const int chunk = pick_chunk(e, item, batch, l);
+    u64* scratch = e.ws.reserve(item * chunk, e.s);
+    for (int b0 = 0; b0 < batch; b0 += chunk) {
+        const int nb = std::min(chunk, batch - b0);
+        BatchPtr lifted = bp_strided(scratch, item);
+        if (c.scheme == SCHEME_BFV) {
+            launch_bfv_scale_up(c.dt, adv(pt, b0), lifted, l, c.bfv_scale_up_consts(level), nb, e.s);
+        } else {
+            launch_lift_ringt(c.dt, adv(pt, b0), lifted, l, nb, e.s);
+            launch_ntt(c.dt, lifted, lifted, rowmap_seq(l, 0, 0, 0, l), nb, false, e.s);
+        }
+        launch_binary(c.dt, subtract ? OP_SUB : OP_ADD, adv(ct, b0), lifted, adv(out, b0),
+                      rowmap_seq(npoly * l, 0, 0, 0, l), l, nb, e.s);
+    }
+}
+void op_mul_plain(OpEnv& e, int level, int npoly, BatchPtr ct, BatchPtr pt, BatchPtr out, int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    Context& c = e.c;
+    const int l = level + 1;
+    if (c.scheme == SCHEME_CKKS) {
+        launch_mul_plain(c.dt, ct, pt, out, npoly, l, false, batch, e.s);
+        return;
+    }
+    // BFV: ciphertext is in the coefficient domain, pt_mul in the NTT domain
+    const size_t item = (size_t)npoly * l * c.N;
+    const int chunk = pick_chunk(e, item, batch, npoly * l);
+    u64* scratch = e.ws.reserve(item * chunk, e.s);
+    for (int b0 = 0; b0 < batch; b0 += chunk) {
+        const int nb = std::min(chunk, batch - b0);
+        BatchPtr t = bp_strided(scratch, item);
+        launch_ntt(c.dt, adv(ct, b0), t, rowmap_seq(npoly * l, 0, 0, 0, l), nb, false, e.s);
+        launch_mul_plain(c.dt, t, adv(pt, b0), t, npoly, l, false, nb, e.s);
+        launch_ntt(c.dt, t, adv(out, b0), rowmap_seq(npoly * l, 0, 0, 0, l), nb, true, e.s);
+    }
+}
+void op_mul_plain_ringt(OpEnv& e, int level, int npoly, BatchPtr ct, BatchPtr pt, BatchPtr out, int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    Context& c = e.c;
+    const int l = level + 1;
+    const size_t item = (size_t)(1 + npoly) * l * c.N;
+    const int chunk = pick_chunk(e, item, batch, (1 + npoly) * l);
+    u64* scratch = e.ws.reserve(item * chunk, e.s);
+    for (int b0 = 0; b0 < batch; b0 += chunk) {
+        const int nb = std::min(chunk, batch - b0);
+        BatchPtr ptm = bp_strided(scratch, item);
+        BatchPtr t = bp_strided(scratch + (size_t)l * c.N, item);
+        launch_lift_ringt(c.dt, adv(pt, b0), ptm, l, nb, e.s);
+        launch_ntt(c.dt, ptm, ptm, rowmap_seq(l, 0, 0, 0, l), nb, false, e.s);
+        if (c.scheme == SCHEME_CKKS) {
+            launch_mul_plain(c.dt, adv(ct, b0), ptm, adv(out, b0), npoly, l, false, nb, e.s);
+        } else {
+            launch_ntt(c.dt, adv(ct, b0), t, rowmap_seq(npoly * l, 0, 0, 0, l), nb, false, e.s);
+            launch_mul_plain(c.dt, t, ptm, t, npoly, l, false, nb, e.s);
+            launch_ntt(c.dt, t, adv(out, b0), rowmap_seq(npoly * l, 0, 0, 0, l), nb, true, e.s);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// fused chains
+// ---------------------------------------------------------------------------------------------
+static void mult_relin_chain(OpEnv& e, int level, BatchPtr a, BatchPtr b, const u64* rlk, int key_level, BatchPtr out2,
+                             int batch, bool rescale) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    Context& c = e.c;
+    const int l = level + 1;
+    const size_t N = c.N;
+    const int mult_limbs = c.scheme == SCHEME_BFV ? bfv_mult_scratch_limbs(c, level) : 0;
+    const int rest = std::max(relin_scratch_limbs(c, level), rescale ? rescale_scratch_limbs(c, level, 2) : 0);
+    // [ct3 | ct2 (only when rescaling) | max(mult, relin, rescale) scratch]
+    const int head = 3 * l + (rescale ? 2 * l : 0);
+    const size_t item = (size_t)(head + std::max(mult_limbs, rest)) * N;
+    const int chunk = pick_chunk(e, item, batch, c.beta(level) * (l + c.np) - l);
+    u64* scratch = e.ws.reserve(item * chunk, e.s);
+    for (int b0 = 0; b0 < batch; b0 += chunk) {
+        const int nb = std::min(chunk, batch - b0);
+        BatchPtr ct3 = bp_strided(scratch, item);
+        BatchPtr ct2 = rescale ? bp_strided(scratch + (size_t)3 * l * N, item) : adv(out2, b0);
+        u64* sub = scratch + (size_t)head * N;
+        if (c.scheme == SCHEME_CKKS) ckks_tensor(e, level, adv(a, b0), adv(b, b0), ct3, nb);
+        else bfv_mult_impl(e, level, adv(a, b0), adv(b, b0), ct3, sub, item, nb);
+        relin_impl(e, level, ct3, rlk, key_level, ct2, sub, item, nb);
+        if (rescale) rescale_impl(e, level, 2, ct2, adv(out2, b0), sub, item, nb);
+    }
+}
+void op_mult_relin(OpEnv& e, int level, BatchPtr a, BatchPtr b, const u64* rlk, int key_level, BatchPtr out2,
+                   int batch) {
+    mult_relin_chain(e, level, a, b, rlk, key_level, out2, batch, false);
+}
+void op_mult_relin_rescale(OpEnv& e, int level, BatchPtr a, BatchPtr b, const u64* rlk, int key_level, BatchPtr out2,
+                           int batch) {
+    mult_relin_chain(e, level, a, b, rlk, key_level, out2, batch, true);
+}
+
+void op_ntt(OpEnv& e, BatchPtr in, BatchPtr out, int rows, const int* mod_idx, int period, bool inverse, int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    LSB_CHECK(rows <= kMaxRows && period >= 1, "lsb: op_ntt rows/period out of range");
+    RowMap m;
+    m.n = rows;
+    for (int r = 0; r < rows; r++) {
+        m.in_slot[r] = m.out_slot[r] = (uint8_t)r;
+        LSB_CHECK(mod_idx[r % period] >= 0 && mod_idx[r % period] < e.c.dt.nmod, "lsb: modulus index out of range");
+        m.mod[r] = (uint8_t)mod_idx[r % period];
+    }
+    launch_ntt(e.c.dt, in, out, m, batch, inverse, e.s);
+}
+
+}  // namespace lsb

@@ -1,0 +1,69 @@
+// Host-only builders of the per-modulus NTT tables and CRT conversion tables (pure C++; shared by
+// the CUDA context and by tests/emul).
+#pragma once
+#include <cstring>
+#include "lsb_kernels.h"
+#include "lsb_host_math.h"
+
+namespace lsb {
+
+// fwd/inv: N entries each.  psi = g^((q-1)/2N), g the smallest generator of Z_q^* (Lattigo ring.NTT
+// parameters); tables hold psi^bitrev(j) / psi^-bitrev(j) with Shoup companions.
+inline void build_ntt_tables(u64 qq, int logN, Tw* f, Tw* iv, ModConst* mc) {
+    using namespace host;
+    const u64 N = 1ull << logN;
+    LSB_CHECK(qq < (1ull << 62), "lsb: modulus must be below 2^62");
+    LSB_CHECK((qq - 1) % (2 * N) == 0 && miller_rabin(qq), "lsb: modulus is not an NTT-friendly prime");
+    const u64 g = smallest_generator(qq);
+    const u64 psi = powmod(g, (qq - 1) / (2 * N), qq);
+    const u64 ipsi = invmod(psi, qq);
+    u64 pw = 1, ipw = 1;
+    for (u64 j = 0; j < N; j++) {
+        const u64 r = bitrev(j, logN);
+        f[r] = make_tw(pw, qq);
+        iv[r] = make_tw(ipw, qq);
+        pw = mulmod(pw, psi, qq);
+        ipw = mulmod(ipw, ipsi, qq);
+    }
+    const u64 ninv = invmod(N % qq, qq);
+    mc->q = qq;
+    mc->bq = make_barrett(qq);
+    mc->ninv = make_tw(ninv, qq);
+    mc->w_ninv = make_tw(mulmod(iv[1].w, ninv, qq), qq);
+}
+
+// CRT tables for extending residues from the moduli `src` to each modulus of `dst` (indices into `moduli`).
+inline BexJob make_bex_tables(const std::vector<u64>& moduli, const std::vector<int>& src, const std::vector<int>& dst) {
+    using namespace host;
+    BexJob j;
+    std::memset(&j, 0, sizeof(j));
+    LSB_CHECK((int)src.size() <= kBexMaxSrc && (int)dst.size() <= kBexMaxDst, "lsb: basis extension too wide");
+    j.ns = (int)src.size();
+    j.nt = (int)dst.size();
+    j.mode = BEX_PLAIN;
+    for (int i = 0; i < j.ns; i++) {
+        const u64 si = moduli[src[i]];
+        j.src_mod[i] = (uint8_t)src[i];
+        j.s_f64[i] = (double)si;
+        u64 prod = 1;
+        for (int k = 0; k < j.ns; k++)
+            if (k != i) prod = mulmod(prod, moduli[src[k]] % si, si);
+        j.qhat_inv[i] = make_tw(invmod(prod, si), si);
+    }
+    for (int tt = 0; tt < j.nt; tt++) {
+        const u64 pj = moduli[dst[tt]];
+        j.dst_mod[tt] = (uint8_t)dst[tt];
+        u64 all = 1;
+        for (int k = 0; k < j.ns; k++) all = mulmod(all, moduli[src[k]] % pj, pj);
+        for (int v = 0; v <= j.ns; v++) j.vS[tt][v] = mulmod((u64)v % pj, all, pj);
+        for (int i = 0; i < j.ns; i++) {
+            u64 prod = 1;
+            for (int k = 0; k < j.ns; k++)
+                if (k != i) prod = mulmod(prod, moduli[src[k]] % pj, pj);
+            j.qhat_mod[tt][i] = prod;
+        }
+    }
+    return j;
+}
+
+}  // namespace lsb

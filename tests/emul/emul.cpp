@@ -1,0 +1,169 @@
+// TEST INFRASTRUCTURE: runs the LSB_HD round / per-coefficient code of lattisense_b200/csrc on the
+// CPU (thread loops in place of CTAs) so that indexing, twiddle selection, lazy ranges and the
+// CRT tables can be checked against the oracle without a GPU.  Never used by the product path.
+#include <vector>
+#include <cstring>
+#include "../../lattisense_b200/csrc/lsb_ntt_core.h"
+#include "../../lattisense_b200/csrc/lsb_tables.h"
+#include "../../lattisense_b200/csrc/lsb_elem_core.h"
+
+using namespace lsb;
+
+template <bool INV>
+static void round_dyn(int lr, int src, int dst, bool fin, bool vec, u64* sm, const u64* gsrc, u64* gdst, TileGeom tg,
+                      const Tw* tw, int g, int loggc, int v, u32 twbase, const ModConst& mc) {
+#define CASE(LR, S, D, F, V)                                                                                   \
+    if (lr == LR && src == S && dst == D && fin == F && vec == V) {                                            \
+        if (!INV) fwd_round<LR, S, D, F, V>(sm, gsrc, gdst, tg, tw, g, loggc, v, twbase, mc.q);                \
+        else inv_round<LR, S, D, F, V>(sm, gsrc, gdst, tg, tw, g, loggc, v, twbase, mc.q, mc.ninv, mc.w_ninv); \
+        return;                                                                                                \
+    }
+#define CASES_LR(LR)                                                                         \
+    CASE(LR, 0, 0, false, false) CASE(LR, 0, 0, false, true) CASE(LR, 0, 0, true, false)     \
+    CASE(LR, 0, 0, true, true) CASE(LR, 1, 0, false, false) CASE(LR, 0, 1, false, false)     \
+    CASE(LR, 0, 1, true, false) CASE(LR, 1, 0, true, false) CASE(LR, 1, 1, false, false) CASE(LR, 1, 1, true, false)
+    CASES_LR(1) CASES_LR(2) CASES_LR(3) CASES_LR(4)
+    throw std::runtime_error("emul: unhandled round configuration");
+}
+
+static void single_pass(int logN, const Tw* f, const Tw* iv, const ModConst& mc, u64* data, bool inverse, int NT) {
+    const int N = 1 << logN;
+    std::vector<u64> sm(N);
+    const Plan P = make_plan(logN, 0);
+    const TileGeom tg{0, 0};
+    if (!inverse) {
+        for (int i = 0; i < P.nrounds; i++) {
+            const int lr = P.rounds[i].lr, loggc = plan_loggc(P, i);
+            for (int tid = 0; tid < NT; tid++)
+                for (int g = tid; g < (N >> lr); g += NT)
+                    round_dyn<false>(lr, i == 0 ? IO_GLOBAL : IO_SMEM, IO_SMEM, i == P.nrounds - 1, loggc == 0, sm.data(),
+                                     data, nullptr, tg, f, g, loggc, P.rounds[i].v, 1u, mc);
+        }
+        for (int c = 0; c < N / 2; c++) {
+            data[2 * c] = sm[swz(2 * c)];
+            data[2 * c + 1] = sm[swz(2 * c) + 1];
+        }
+    } else {
+        for (int c = 0; c < N / 2; c++) {
+            sm[swz(2 * c)] = data[2 * c];
+            sm[swz(2 * c) + 1] = data[2 * c + 1];
+        }
+        for (int j = 0; j < P.nrounds; j++) {
+            const int i = P.nrounds - 1 - j;
+            const int lr = P.rounds[i].lr, loggc = plan_loggc(P, i);
+            for (int tid = 0; tid < NT; tid++)
+                for (int g = tid; g < (N >> lr); g += NT)
+                    round_dyn<true>(lr, IO_SMEM, i == 0 ? IO_GLOBAL : IO_SMEM, i == 0, loggc == 0, sm.data(), nullptr,
+                                    data, tg, iv, g, loggc, P.rounds[i].v, 1u, mc);
+        }
+    }
+}
+
+// mirrors k_ntt_cols / k_ntt_rows (kRowLS = 8, kColLC = 4, kRowSub = 16)
+static void cols_pass(int logN, const Tw* tw, const ModConst& mc, u64* data, bool inverse) {
+    const int LA = logN - 8, LC = 4, T = 1 << (LA + LC), NT = T / 16, UNITS = 256 >> LC;
+    const Plan P = make_plan(LA, LC);
+    const TileGeom tg{LC, 8};
+    std::vector<u64> sm(T);
+    for (int cb = 0; cb < UNITS; cb++) {
+        u64* base = data + (cb << LC);
+        for (int j = 0; j < P.nrounds; j++) {
+            const int i = inverse ? P.nrounds - 1 - j : j;
+            const int lr = P.rounds[i].lr, loggc = plan_loggc(P, i);
+            const int src = j == 0 ? IO_GLOBAL : IO_SMEM, dst = j == P.nrounds - 1 ? IO_GLOBAL : IO_SMEM;
+            // a round reading global and writing global in place is only safe because reads precede writes per group
+            for (int tid = 0; tid < NT; tid++)
+                for (int g = tid; g < (T >> lr); g += NT) {
+                    if (!inverse) round_dyn<false>(lr, src, dst, false, false, sm.data(), base, base, tg, tw, g, loggc, P.rounds[i].v, 1u, mc);
+                    else round_dyn<true>(lr, src, dst, i == 0, false, sm.data(), base, base, tg, tw, g, loggc, P.rounds[i].v, 1u, mc);
+                }
+        }
+    }
+}
+static void rows_pass(int logN, const Tw* tw, const ModConst& mc, u64* data, bool inverse) {
+    const int N = 1 << logN, LA = logN - 8, S = 256, SUB = 16, T = S * SUB, UNITS = N / T;
+    const TileGeom tg{0, 0};
+    std::vector<u64> sm(T);
+    for (int tb = 0; tb < UNITS; tb++) {
+        u64* base = data + (size_t)tb * T;
+        if (inverse)
+            for (int c = 0; c < T / 2; c++) {
+                sm[swz(2 * c)] = base[2 * c];
+                sm[swz(2 * c) + 1] = base[2 * c + 1];
+            }
+        for (int phase = 0; phase < 2; phase++)
+            for (int tid = 0; tid < 256; tid++) {
+                const int st = tid >> 4, g = tid & 15;
+                const u32 twbase = (1u << LA) + (u32)(tb * SUB + st);
+                u64* smt = sm.data() + st * S;
+                if (!inverse) {
+                    if (phase == 0) round_dyn<false>(4, IO_GLOBAL, IO_SMEM, false, false, smt, base + st * S, nullptr, tg, tw, g, 4, 0, twbase, mc);
+                    else round_dyn<false>(4, IO_SMEM, IO_SMEM, true, true, smt, nullptr, nullptr, tg, tw, g, 0, 4, twbase, mc);
+                } else {
+                    if (phase == 0) round_dyn<true>(4, IO_SMEM, IO_SMEM, false, true, smt, nullptr, nullptr, tg, tw, g, 0, 4, twbase, mc);
+                    else round_dyn<true>(4, IO_SMEM, IO_GLOBAL, false, false, smt, nullptr, base + st * S, tg, tw, g, 4, 0, twbase, mc);
+                }
+            }
+        if (!inverse)
+            for (int c = 0; c < T / 2; c++) {
+                base[2 * c] = sm[swz(2 * c)];
+                base[2 * c + 1] = sm[swz(2 * c) + 1];
+            }
+    }
+}
+
+extern "C" {
+
+int emul_ntt(int logN, u64 q, u64* data, int inverse, int nthreads) {
+    try {
+        const int N = 1 << logN;
+        std::vector<Tw> f(N), iv(N);
+        ModConst mc;
+        build_ntt_tables(q, logN, f.data(), iv.data(), &mc);
+        if (logN <= 14) {
+            single_pass(logN, f.data(), iv.data(), mc, data, inverse != 0, nthreads);
+        } else if (!inverse) {
+            cols_pass(logN, f.data(), mc, data, false);
+            rows_pass(logN, f.data(), mc, data, false);
+        } else {
+            rows_pass(logN, iv.data(), mc, data, true);
+            cols_pass(logN, iv.data(), mc, data, true);
+        }
+        return 0;
+    } catch (const std::exception& e) {
+        fprintf(stderr, "emul_ntt: %s\n", e.what());
+        return 1;
+    }
+}
+
+// moduli[nmod]; src/dst index lists; in [ns][N], out [nt][N]; mode/centered as BexJob; other [nt][N] (mode 1)
+int emul_basis_extend(int logN, const u64* moduli, int nmod, const int* src, int ns, const int* dst, int nt, int centered,
+                      const u64* in, u64* out) {
+    try {
+        const int N = 1 << logN;
+        std::vector<u64> mods(moduli, moduli + nmod);
+        std::vector<ModConst> mc(nmod);
+        for (int m = 0; m < nmod; m++) {
+            mc[m].q = mods[m];
+            mc[m].bq = host::make_barrett(mods[m]);
+        }
+        BexJob job = make_bex_tables(mods, std::vector<int>(src, src + ns), std::vector<int>(dst, dst + nt));
+        job.centered = centered;
+        for (int j = 0; j < N; j++) {
+            u64 x[kBexMaxSrc];
+            for (int i = 0; i < ns; i++) x[i] = in[(size_t)i * N + j];
+            bex_coeff(job, mc.data(), x, [&](int) { return (u64)0; }, [&](int t, u64 v) { out[(size_t)t * N + j] = v; });
+        }
+        return 0;
+    } catch (const std::exception& e) {
+        fprintf(stderr, "emul_basis_extend: %s\n", e.what());
+        return 1;
+    }
+}
+
+// a*b mod q through the device Barrett path, and 128-bit accumulate path
+u64 emul_mulmod(u64 a, u64 b, u64 q) { return mulmod(a, b, host::make_barrett(q)); }
+u64 emul_barrett64(u64 a, u64 q) { return barrett64(a, host::make_barrett(q)); }
+u64 emul_mul_shoup(u64 a, u64 w, u64 q) { return mul_shoup(a, host::make_tw(w, q), q); }
+
+}  // extern "C"

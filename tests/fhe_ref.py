@@ -95,10 +95,11 @@ _BTP_Q = [0x10000000006E0001, 0x10000140001, 0xFFFFE80001, 0xFFFFC40001, 0x10000
 _BTP_P = [0x1FFFFFFFFFE00001, 0x1FFFFFFFFFC80001, 0x1FFFFFFFFFB40001, 0x1FFFFFFFFF500001, 0x1FFFFFFFFF420001]
 CKKS_BTP_N16 = Params("ckks_btp_n65536", SCHEME_CKKS, 16, _BTP_Q, _BTP_P, scale=2.0 ** 40)
 CKKS_BTP_N13 = Params("ckks_btp_toy_n8192", SCHEME_CKKS, 13, _BTP_Q, _BTP_P, scale=2.0 ** 40)
+CKKS_BTP_N15 = Params("ckks_btp_n32768", SCHEME_CKKS, 15, _BTP_Q, _BTP_P, scale=2.0 ** 40)
 # small-ring variants (not NTT-friendly for every reference prime, so use the n=8192 sets' primes: = 1 mod 2^14)
 CKKS_N12 = Params("ckks_small_n4096", SCHEME_CKKS, 12, CKKS_N13.q[:4], CKKS_N13.p, scale=2.0 ** 30)
 
-ALL_PARAMS = {p.name: p for p in (BFV_N14, BFV_N13, CKKS_N14, CKKS_N13, CKKS_BTP_N16, CKKS_BTP_N13, CKKS_N12)}
+ALL_PARAMS = {p.name: p for p in (BFV_N14, BFV_N13, CKKS_N14, CKKS_N13, CKKS_BTP_N16, CKKS_BTP_N13, CKKS_BTP_N15, CKKS_N12)}
 
 
 # ---------------------------------------------------------------------------------------------

@@ -1,0 +1,101 @@
+"""CPU checks of the device code's LSB_HD bodies (NTT rounds, basis extension, Barrett/Shoup)
+against the oracle — no GPU needed.  These validate indexing/twiddle/range logic of the kernels;
+the GPU parity tests proper are in test_gpu_parity.py."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import fhe_ref as R
+
+CASES = [
+    (R.CKKS_N12, [0, 3, 4], 256),
+    (R.CKKS_N13, [0, 5, 6], 256),
+    (R.CKKS_N14, [0, 1, 10, 11], 512),
+    (R.BFV_N14, [0, 5, 7], 512),
+    (R.BFV_N13, [0, 3], 256),
+    (R.CKKS_BTP_N16, [0, 1, 29], 0),
+    (R.CKKS_BTP_N15, [0, 12, 25], 0),
+]
+
+
+@pytest.mark.parametrize("params,mids,nt", CASES, ids=[c[0].name for c in CASES])
+def test_ntt_rounds_match_oracle(emul, params, mids, nt):
+    rng = np.random.default_rng(7)
+    o = R.Oracle(params)
+    for mid in mids:
+        q = o.moduli[mid]
+        a = rng.integers(0, q, size=params.N, dtype=np.uint64)
+        a[:4] = [0, 1, q - 1, q // 2]
+        fwd = a.copy()
+        assert emul.emul_ntt(params.logN, q, R.P(fwd), 0, nt) == 0
+        assert np.array_equal(fwd, o.ntt(mid, a))
+        inv = a.copy()
+        assert emul.emul_ntt(params.logN, q, R.P(inv), 1, nt) == 0
+        assert np.array_equal(inv, o.ntt(mid, a, inverse=True))
+        back = fwd.copy()
+        emul.emul_ntt(params.logN, q, R.P(back), 1, nt)
+        assert np.array_equal(back, a)
+
+
+def test_ntt_thread_count_independent(emul):
+    rng = np.random.default_rng(3)
+    p = R.CKKS_N13
+    q = p.q[1]
+    a = rng.integers(0, q, size=p.N, dtype=np.uint64)
+    outs = []
+    for nt in (64, 256, 512, 1024):
+        x = a.copy()
+        emul.emul_ntt(p.logN, q, R.P(x), 0, nt)
+        outs.append(x)
+    for x in outs[1:]:
+        assert np.array_equal(x, outs[0])
+
+
+@pytest.mark.parametrize("params", [R.CKKS_N13, R.BFV_N14, R.CKKS_BTP_N13], ids=lambda p: p.name)
+def test_basis_extend_matches_oracle(emul, params):
+    rng = np.random.default_rng(11)
+    o = R.Oracle(params)
+    mods = np.array(o.moduli, dtype=np.uint64)
+    nq, k = len(params.q), params.k
+    combos = [(list(range(0, min(k, nq))), [i for i in range(nq) if i >= k] + [nq + j for j in range(k)], 0),
+              ([nq + j for j in range(k)], list(range(nq)), 0),
+              ([nq - 1], list(range(nq - 1)) + [nq + j for j in range(k)], 1)]
+    if params.scheme == R.SCHEME_BFV:
+        nqm = o.nmods - nq - k
+        combos.append((list(range(nq)), [nq + k + j for j in range(nqm)], 0))
+        combos.append(([nq + k + j for j in range(nqm)], list(range(nq)), 0))
+    for src, dst, centered in combos:
+        src, dst = src[:16], dst[:48]
+        x = np.stack([rng.integers(0, o.moduli[i], size=params.N, dtype=np.uint64) for i in src])
+        if not centered:
+            want = o.basis_extend(src, x, dst)
+        else:
+            s = o.moduli[src[0]]
+            want = np.zeros((len(dst), params.N), dtype=np.uint64)
+            xs = x[0].astype(object)
+            for t, d in enumerate(dst):
+                pj = o.moduli[d]
+                want[t] = np.array([(int(v) % pj) if int(v) < (s >> 1) else (-(s - int(v)) % pj) for v in xs],
+                                   dtype=np.uint64)
+        got = np.zeros((len(dst), params.N), dtype=np.uint64)
+        sa = (C.c_int * len(src))(*src)
+        da = (C.c_int * len(dst))(*dst)
+        assert emul.emul_basis_extend(params.logN, R.P(mods), len(mods), sa, len(src), da, len(dst), centered,
+                                      R.P(x), R.P(got)) == 0
+        assert np.array_equal(got, want), (src, dst, centered)
+
+
+def test_barrett_and_shoup(emul):
+    rng = np.random.default_rng(5)
+    for q in [R.CKKS_N14.q[0], R.CKKS_N14.q[1], R.BFV_N14.q[0], R.CKKS_BTP_N16.p[0], 65537]:
+        for _ in range(2000):
+            a = int(rng.integers(0, q))
+            b = int(rng.integers(0, q))
+            assert emul.emul_mulmod(a, b, q) == a * b % q
+            assert emul.emul_mul_shoup(a, b, q) == a * b % q
+            x = int(rng.integers(0, 2 ** 63)) * 2 + int(rng.integers(0, 2))
+            assert emul.emul_barrett64(x, q) == x % q
+            assert emul.emul_mul_shoup(x, b, q) == x * b % q
+        for a, b in [(0, 0), (q - 1, q - 1), (1, q - 1), (q - 1, 1)]:
+            assert emul.emul_mulmod(a, b, q) == a * b % q

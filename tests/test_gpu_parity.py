@@ -1,0 +1,270 @@
+"""GPU parity tests: every output limb of the CUDA path (called through the C ABI in
+include/lsb200.h) must equal the CPU oracle bit for bit on the same seeded inputs.
+
+Reference test cases mirrored (unittests/test_gpu_bfv.cpp / test_gpu_ckks.cpp, decode-level there):
+cmc, cmc_relin (:314), cmc_relin_rescale (:340), rescale, drop_level, rotate_col (:459),
+advanced_rotate_col (:493), rotate_row (:530), cac/csc/cneg, cap/csp, cmp.  The reference compares
+decoded messages only; limb equality against the oracle is the stricter bar set by BASELINE.json.
+"""
+import numpy as np
+import pytest
+
+import fhe_ref as R
+
+pytestmark = pytest.mark.gpu
+
+
+def _ctx(params):
+    import lattisense_b200 as L
+    return L.Context(params.scheme, params.logN, params.q, params.p, params.t)
+
+
+_cache = {}
+
+
+def env(params):
+    """(oracle, gpu context, secret) per parameter set, cached for the session."""
+    if params.name not in _cache:
+        o = R.Oracle(params)
+        _cache[params.name] = (o, _ctx(params), o.gen_secret(1234))
+    return _cache[params.name]
+
+
+def rand_ct(o, rng, level, npoly=2, batch=None):
+    shape = (npoly, level + 1, o.N) if batch is None else (batch, npoly, level + 1, o.N)
+    out = np.zeros(shape, dtype=np.uint64)
+    for i in range(level + 1):
+        out[..., i, :] = rng.integers(0, o.p.q[i], size=shape[:-2] + (o.N,), dtype=np.uint64)
+    return out
+
+
+def rand_evk(o, rng, key_level):
+    shape = o.evk_shape(key_level)
+    out = np.zeros(shape, dtype=np.uint64)
+    mods = o.p.q[:key_level + 1] + o.p.p
+    for i, m in enumerate(mods):
+        out[:, :, i, :] = rng.integers(0, m, size=(shape[0], 2, o.N), dtype=np.uint64)
+    return out
+
+
+SETS = [R.CKKS_N12, R.CKKS_N13, R.CKKS_N14, R.BFV_N13, R.BFV_N14]
+IDS = [p.name for p in SETS]
+
+
+@pytest.mark.parametrize("params", SETS + [R.CKKS_BTP_N15, R.CKKS_BTP_N16], ids=IDS + ["btp_n32768", "btp_n65536"])
+def test_ntt_parity_all_moduli(params):
+    o, g, _ = env(params)
+    rng = np.random.default_rng(21)
+    nm = o.nmods if params.logN <= 14 else 8
+    mids = list(range(nm)) if params.logN <= 14 else [0, 1, 9, 12, 24, 25, 27, 29]
+    a = np.stack([rng.integers(0, o.moduli[m], size=o.N, dtype=np.uint64) for m in mids])
+    a[:, :3] = 0
+    a[0, :3] = [1, o.moduli[mids[0]] - 1, 2]
+    batch = np.stack([a, a[:, ::-1].copy(), np.roll(a, 17, axis=1)])
+    fwd = g.ntt(batch, mids)
+    inv = g.ntt(batch, mids, inverse=True)
+    for b in range(3):
+        for r, m in enumerate(mids):
+            assert np.array_equal(fwd[b, r], o.ntt(m, batch[b, r])), (b, m)
+            assert np.array_equal(inv[b, r], o.ntt(m, batch[b, r], inverse=True)), (b, m)
+    assert np.array_equal(g.ntt(fwd, mids, inverse=True), batch)
+
+
+@pytest.mark.parametrize("params", SETS, ids=IDS)
+def test_mult_relin_rescale_parity(params):
+    o, g, s = env(params)
+    rng = np.random.default_rng(31)
+    L = params.max_level
+    rlk = o.gen_rlk(s, 77, L)
+    for level in sorted({L, max(1, L // 2), 1}):
+        a, b = rand_ct(o, rng, level), rand_ct(o, rng, level)
+        want3 = o.mult(a, b)
+        got3 = g.mult(a, b)
+        assert np.array_equal(got3, want3), ("mult", level)
+        want2 = o.relin(want3, rlk)
+        assert np.array_equal(g.relin(want3, rlk), want2), ("relin", level)
+        want1 = o.rescale(want2)
+        assert np.array_equal(g.rescale(want2), want1), ("rescale", level)
+        assert np.array_equal(g.rescale(want3), o.rescale(want3)), ("rescale ct3", level)
+        assert np.array_equal(g.mult_relin(a, b, rlk), want2), ("mult_relin", level)
+        assert np.array_equal(g.mult_relin(a, b, rlk, rescale=True), want1), ("mult_relin_rescale", level)
+        assert np.array_equal(g.drop_level(a), o.drop_level(a))
+
+
+@pytest.mark.parametrize("params", SETS, ids=IDS)
+def test_rotate_parity(params):
+    o, g, s = env(params)
+    rng = np.random.default_rng(41)
+    L = params.max_level
+    for step, level in [(1, L), (3, max(1, L - 1)), (-5, 1)]:
+        gal = R.galois_for_col_step(o.N, step)
+        glk = o.gen_glk(s, 90 + step, L, gal)
+        ct = rand_ct(o, rng, level)
+        assert np.array_equal(g.rotate(ct, glk, gal), o.rotate(ct, glk, gal)), (step, level)
+    gal = R.galois_for_row(o.N)
+    glk = rand_evk(o, rng, L)
+    ct = rand_ct(o, rng, L)
+    assert np.array_equal(g.rotate(ct, glk, gal), o.rotate(ct, glk, gal))
+
+
+@pytest.mark.parametrize("params", [R.CKKS_N13, R.BFV_N13], ids=["ckks", "bfv"])
+def test_batched_and_ragged_chunks(params):
+    """batch sizes that do not divide the chunk, chunk = 1, and batch = 1 all give per-item oracle results"""
+    o, g, s = env(params)
+    rng = np.random.default_rng(51)
+    L = params.max_level
+    rlk = rand_evk(o, rng, L)
+    B = 5
+    a, b = rand_ct(o, rng, L, batch=B), rand_ct(o, rng, L, batch=B)
+    want = np.stack([o.rescale(o.relin(o.mult(a[i], b[i]), rlk)) for i in range(B)])
+    gal = R.galois_for_col_step(o.N, 2)
+    want_rot = np.stack([o.rotate(a[i], rlk, gal) for i in range(B)])
+    try:
+        for chunk in (0, 1, 2, 3, 7):
+            g.set_chunk(chunk)
+            assert np.array_equal(g.mult_relin(a, b, rlk, rescale=True), want), chunk
+            assert np.array_equal(g.rotate(a, rlk, gal), want_rot), chunk
+    finally:
+        g.set_chunk(0)
+
+
+@pytest.mark.parametrize("params", SETS, ids=IDS)
+def test_add_sub_neg_parity(params):
+    o, g, _ = env(params)
+    rng = np.random.default_rng(61)
+    L = params.max_level
+    a, b = rand_ct(o, rng, L, batch=2), rand_ct(o, rng, L, batch=2)
+    a[0, 0, 0, :4] = 0
+    b[0, 0, 0, :4] = 0
+    for i in range(2):
+        assert np.array_equal(g.add(a, b)[i], o.add(a[i], b[i]))
+        assert np.array_equal(g.sub(a, b)[i], o.sub(a[i], b[i]))
+        assert np.array_equal(g.neg(a)[i], o.neg(a[i]))
+    a3 = rand_ct(o, rng, 1, npoly=3)
+    assert np.array_equal(g.add(a3, a3), o.add(a3, a3))
+
+
+@pytest.mark.parametrize("params", SETS, ids=IDS)
+def test_plain_ops_parity(params):
+    """ct +- pt, ct x pt_mul, ct (+,x) pt_ringt against the oracle's limb arithmetic"""
+    o, g, _ = env(params)
+    rng = np.random.default_rng(71)
+    level = min(2, params.max_level)
+    l = level + 1
+    ct = rand_ct(o, rng, level)
+    pt = rand_ct(o, rng, level, npoly=1)[0]
+    want = ct.copy()
+    want[0] = o.add(ct[:1], pt[None])[0]
+    assert np.array_equal(g.add_plain(ct, pt), want)
+    want[0] = o.sub(ct[:1], pt[None])[0]
+    assert np.array_equal(g.add_plain(ct, pt, subtract=True), want)
+
+    def mulmod_limbs(x, y):
+        out = np.zeros_like(x)
+        for i in range(l):
+            q = params.q[i]
+            out[:, i] = np.array([[int(u) * int(v) % q for u, v in zip(xr, y[i])] for xr in x[:, i]], dtype=np.uint64)
+        return out
+
+    ntt_dom = params.scheme == R.SCHEME_CKKS
+    ct_n = ct if ntt_dom else o.ntt_limbs(ct)
+    prod = mulmod_limbs(ct_n, pt)
+    want_mul = prod if ntt_dom else o.ntt_limbs(prod, inverse=True)
+    assert np.array_equal(g.mul_plain(ct, pt), want_mul)
+
+    t = params.t if params.scheme == R.SCHEME_BFV else 65537
+    m = rng.integers(0, t, size=(1, o.N), dtype=np.uint64)
+    lifted = o.ntt_limbs(np.repeat(m, l, axis=0))
+    prod = mulmod_limbs(ct_n, lifted)
+    want_mr = prod if ntt_dom else o.ntt_limbs(prod, inverse=True)
+    assert np.array_equal(g.mul_plain_ringt(ct, m), want_mr)
+    if params.scheme == R.SCHEME_BFV:
+        up = o.bfv_scale_up(level, m[0])
+        want = ct.copy()
+        want[0] = o.add(ct[:1], up[None])[0]
+        assert np.array_equal(g.add_plain_ringt(ct, m), want)
+    else:
+        want = ct.copy()
+        want[0] = o.add(ct[:1], lifted[None])[0]
+        assert np.array_equal(g.add_plain_ringt(ct, m), want)
+
+
+def test_bfv_mult_relin_decrypts_to_product():
+    """reference criterion (unittests/test_gpu_bfv.cpp:314-335): decode(dec(z)) == x*y mod t"""
+    params = R.BFV_N13
+    o, g, s = env(params)
+    rng = np.random.default_rng(81)
+    enc = R.BfvEncoder(params)
+    L = params.max_level
+    x = rng.integers(0, params.t, size=o.N, dtype=np.uint64)
+    y = rng.integers(0, params.t, size=o.N, dtype=np.uint64)
+    cx = o.encrypt(s, 5, L, o.bfv_scale_up(L, enc.encode_coeffs(x)))
+    cy = o.encrypt(s, 6, L, o.bfv_scale_up(L, enc.encode_coeffs(y)))
+    rlk = o.gen_rlk(s, 7, L)
+    z = g.mult_relin(cx, cy, rlk)
+    got = enc.decode_coeffs(R.bfv_decode_pt(o, o.decrypt(s, z)))
+    assert np.array_equal(got, x * y % params.t)
+    gal = R.galois_for_col_step(o.N, 1)
+    glk = o.gen_glk(s, 8, L, gal)
+    r = enc.decode_coeffs(R.bfv_decode_pt(o, o.decrypt(s, g.rotate(cx, glk, gal))))
+    half = o.N // 2
+    want = np.concatenate([np.roll(x[:half], -1), np.roll(x[half:], -1)])
+    assert np.array_equal(r, want)
+
+
+def test_ckks_mult_relin_rescale_precision():
+    """reference criterion (unittests/test_gpu_ckks.cpp:37-43): mean real precision >= 10 bits"""
+    params = R.CKKS_N13
+    o, g, s = env(params)
+    rng = np.random.default_rng(91)
+    L = params.max_level
+    x = rng.uniform(-1, 1, o.N // 2)
+    y = rng.uniform(-1, 1, o.N // 2)
+    cx = o.encrypt(s, 15, L, R.ckks_encode(o, x, L, params.scale))
+    cy = o.encrypt(s, 16, L, R.ckks_encode(o, y, L, params.scale))
+    rlk = o.gen_rlk(s, 17, L)
+    z = g.mult_relin(cx, cy, rlk, rescale=True)
+    scale = params.scale * params.scale / params.q[L]
+    got = R.ckks_decode(o, o.decrypt(s, z), scale)
+    assert R.mean_precision_bits(got, x * y) >= 10.0
+    gal = R.galois_for_col_step(o.N, 3)
+    glk = o.gen_glk(s, 18, L, gal)
+    r = R.ckks_decode(o, o.decrypt(s, g.rotate(cx, glk, gal)), params.scale)
+    assert R.mean_precision_bits(r, np.roll(x, -3)) >= 10.0
+
+
+def test_n65536_keyswitch_parity():
+    """cfg4/cfg5 shapes: N = 2^16 with the 25Q+5P bootstrap chain (frontend/custom_task.py:387-420)"""
+    params = R.CKKS_BTP_N16
+    o, g, s = env(params)
+    rng = np.random.default_rng(101)
+    for level in (2, 24):
+        key_level = 24 if level == 24 else 4
+        evk = rand_evk(o, rng, key_level)
+        a, b = rand_ct(o, rng, level), rand_ct(o, rng, level)
+        ct3 = o.mult(a, b)
+        assert np.array_equal(g.mult(a, b), ct3)
+        want = o.relin(ct3, evk)
+        assert np.array_equal(g.relin(ct3, evk), want), level
+        if level == 2:
+            gal = R.galois_for_col_step(o.N, 16)
+            assert np.array_equal(g.rotate(a, evk, gal), o.rotate(a, evk, gal))
+            assert np.array_equal(g.rescale(want), o.rescale(want))
+
+
+def test_errors_are_reported_not_swallowed():
+    import lattisense_b200 as L
+    params = R.CKKS_N12
+    o, g, _ = env(params)
+    rng = np.random.default_rng(111)
+    ct0 = rand_ct(o, rng, 0)
+    with pytest.raises(L.LsbError):
+        g.rescale(ct0)
+    evk_low = rand_evk(o, rng, 1)
+    ct3 = rand_ct(o, rng, 2, npoly=3)
+    with pytest.raises(L.LsbError):
+        g.relin(ct3, evk_low)
+    with pytest.raises(L.LsbError):
+        L.Context(R.SCHEME_CKKS, 12, [params.q[0] + 2], params.p)
+    with pytest.raises(L.LsbError):
+        L.Context(R.SCHEME_CKKS, 11, params.q, params.p)

@@ -96,6 +96,12 @@ int lsb_mult_relin(lsb_context_t ctx, int level, const uint64_t* d_a, const uint
 int lsb_mult_relin_rescale(lsb_context_t ctx, int level, const uint64_t* d_a, const uint64_t* d_b,
                            const uint64_t* d_rlk, int key_level, uint64_t* d_out2, int batch, void* stream);
 
+/* Launch accounting (always on) and per-kernel-class CUDA-event timing (bench.py roofline pass).
+ * kind: 0 NTT fwd, 1 NTT inv, 2 basis extension, 3 key-switch inner product, 4 other limb-wise kernels. */
+long long lsb_launch_count(lsb_context_t ctx);
+void lsb_profile_enable(lsb_context_t ctx, int on);
+int lsb_profile_read(lsb_context_t ctx, int kind, double* ms, long long* kernels, double* algorithmic_bytes);
+
 #ifdef __cplusplus
 }
 #endif

@@ -69,6 +69,10 @@ def lib():
     L.lsb_mul_plain_ringt.argtypes = [vp, ci, ci, vp, vp, vp, ci, vp]
     L.lsb_mult_relin.argtypes = [vp, ci, vp, vp, vp, ci, vp, ci, vp]
     L.lsb_mult_relin_rescale.argtypes = [vp, ci, vp, vp, vp, ci, vp, ci, vp]
+    L.lsb_launch_count.restype = C.c_longlong
+    L.lsb_launch_count.argtypes = [vp]
+    L.lsb_profile_enable.argtypes = [vp, ci]
+    L.lsb_profile_read.argtypes = [vp, ci, C.POINTER(C.c_double), C.POINTER(C.c_longlong), C.POINTER(C.c_double)]
     _lib = L
     return L
 
@@ -149,6 +153,17 @@ class Context:
 
     def set_chunk(self, chunk):
         lib().lsb_set_chunk(self.h, int(chunk))
+
+    def launch_count(self):
+        return int(lib().lsb_launch_count(self.h))
+
+    def profile(self, on):
+        lib().lsb_profile_enable(self.h, 1 if on else 0)
+
+    def profile_read(self, kind):
+        ms, n, b = C.c_double(), C.c_longlong(), C.c_double()
+        _check(lib().lsb_profile_read(self.h, kind, C.byref(ms), C.byref(n), C.byref(b)))
+        return ms.value, n.value, b.value
 
     def beta(self, level):
         return (level + 1 + self.k - 1) // self.k

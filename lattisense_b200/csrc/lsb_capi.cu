@@ -224,4 +224,19 @@ int lsb_mult_relin_rescale(lsb_context_t h, int level, const uint64_t* d_a, cons
     });
 }
 
+long long lsb_launch_count(lsb_context_t h) { return h && h->c ? h->c->prof.launches.load() : 0; }
+void lsb_profile_enable(lsb_context_t h, int on) {
+    if (!h || !h->c) return;
+    h->c->prof.reset();
+    h->c->prof.enabled.store(on != 0);
+}
+int lsb_profile_read(lsb_context_t h, int kind, double* ms, long long* kernels, double* algorithmic_bytes) {
+    LSB_API_BEGIN
+    LSB_CHECK(h && h->c && kind >= 0 && kind < PK_COUNT, "lsb: bad profile query");
+    LSB_CUDA(cudaSetDevice(h->c->device));
+    h->c->prof.read(kind, ms, kernels, algorithmic_bytes);
+    return 0;
+    LSB_API_END(1)
+}
+
 }  // extern "C"

@@ -65,6 +65,7 @@ Context::Context(int device_, int scheme_, int logN_, const u64* q, int nq_, con
         build_ntt_tables(moduli[m], logN, &fwd[(size_t)m * N], &inv[(size_t)m * N], &mc[m]);
     }
     dt.device = device;
+    dt.prof = &prof;
     cudaDeviceProp prop;
     LSB_CUDA(cudaGetDeviceProperties(&prop, device));
     dt.sm_count = prop.multiProcessorCount;

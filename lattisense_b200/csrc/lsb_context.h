@@ -36,6 +36,7 @@ struct Context {
     std::vector<u64> moduli;      // Q..., P..., QMul...
     std::vector<int> level_qmul;  // BFV: index of the last auxiliary prime used at each level
     DeviceTables dt;
+    Profiler prof;
 
     Context(int device, int scheme, int logN, const u64* q, int nq, const u64* p, int np, u64 t);
     ~Context();

@@ -47,6 +47,7 @@ void launch_binary(const DeviceTables& dt, BinOp op, BatchPtr a, BatchPtr b, Bat
                    int b_rows, int batch, cudaStream_t s) {
     if (batch <= 0 || map.n <= 0) return;
     BinArgs g{a, b, out, dt.N, b_rows, (int)op, dt.mods, map};
+    ProfScope _ps(dt.prof, PK_ELEMWISE, s, 8.0 * dt.N * map.n * batch * 3);
     k_binary<<<elem_grid(dt.N, map.n, batch), kElemThreads, 0, s>>>(g);
     LSB_CUDA(cudaGetLastError());
 }
@@ -70,6 +71,7 @@ __global__ void __launch_bounds__(kElemThreads) k_negate(const __grid_constant__
 void launch_negate(const DeviceTables& dt, BatchPtr a, BatchPtr out, const RowMap& map, int batch, cudaStream_t s) {
     if (batch <= 0 || map.n <= 0) return;
     NegArgs g{a, out, dt.N, dt.mods, map};
+    ProfScope _ps(dt.prof, PK_ELEMWISE, s, 8.0 * dt.N * map.n * batch * 2);
     k_negate<<<elem_grid(dt.N, map.n, batch), kElemThreads, 0, s>>>(g);
     LSB_CUDA(cudaGetLastError());
 }
@@ -127,6 +129,7 @@ void launch_tensor(const DeviceTables& dt, BatchPtr a, BatchPtr b, BatchPtr out,
     g.out_ps = out_poly_stride;
     g.mods = dt.mods;
     for (int i = 0; i < nl; i++) g.mod[i] = mod_of_limb[i];
+    ProfScope _ps(dt.prof, PK_ELEMWISE, s, 8.0 * dt.N * nl * batch * 7);
     k_tensor<<<elem_grid(dt.N, nl, batch), kElemThreads, 0, s>>>(g);
     LSB_CUDA(cudaGetLastError());
 }
@@ -161,6 +164,7 @@ void launch_mul_plain(const DeviceTables& dt, BatchPtr ct, BatchPtr pt, BatchPtr
                       bool accumulate, int batch, cudaStream_t s) {
     if (batch <= 0) return;
     MulPlainArgs g{ct, pt, out, dt.N, npoly, nl, accumulate ? 1 : 0, dt.mods};
+    ProfScope _ps(dt.prof, PK_ELEMWISE, s, 8.0 * dt.N * nl * batch * (1 + 2 * npoly));
     k_mul_plain<<<elem_grid(dt.N, nl, batch), kElemThreads, 0, s>>>(g);
     LSB_CUDA(cudaGetLastError());
 }
@@ -193,6 +197,7 @@ void launch_basis_extend(const DeviceTables& dt, const BexJob* jobs, int njobs, 
     if (batch <= 0 || njobs <= 0) return;
     BexArgs g{jobs, src, dst, other, dt.N, dt.mods};
     dim3 grid((dt.N + kElemThreads - 1) / kElemThreads, njobs, batch);
+    ProfScope _ps(dt.prof, PK_BASIS_EXT, s, 0.0);
     k_basis_extend<<<grid, kElemThreads, 0, s>>>(g);
     LSB_CUDA(cudaGetLastError());
 }
@@ -227,6 +232,7 @@ void launch_finish(const DeviceTables& dt, BatchPtr a, BatchPtr b, BatchPtr adde
                    const FinishMap* fm_dev, int nrows, int batch, cudaStream_t s) {
     if (batch <= 0 || nrows <= 0) return;
     FinishArgs g{a, b, addend, out, fm_dev, dt.N, has_addend ? 1 : 0, dt.mods};
+    ProfScope _ps(dt.prof, PK_ELEMWISE, s, 8.0 * dt.N * nrows * batch * 4);
     k_finish<<<elem_grid(dt.N, nrows, batch), kElemThreads, 0, s>>>(g);
     LSB_CUDA(cudaGetLastError());
 }
@@ -271,6 +277,7 @@ __global__ void __launch_bounds__(kElemThreads) k_ks_inner(const __grid_constant
 void launch_ks_inner(const DeviceTables& dt, const KsInnerArgs& a, int batch, cudaStream_t s) {
     if (batch <= 0) return;
     KsInnerK g{a, dt.N, dt.mods};
+    ProfScope _ps(dt.prof, PK_KS_INNER, s, 8.0 * dt.N * (a.l + a.k) * (batch * (a.beta + 2.0) + 2.0 * a.beta));
     k_ks_inner<<<elem_grid(dt.N, a.l + a.k, batch), kElemThreads, 0, s>>>(g);
     LSB_CUDA(cudaGetLastError());
 }
@@ -304,6 +311,7 @@ void launch_rescale_lift(const DeviceTables& dt, BatchPtr last, int last_poly_st
                          int batch, cudaStream_t s) {
     if (batch <= 0) return;
     RescaleLiftArgs g{last, tmp, dt.N, npoly, level, last_poly_stride, dt.mods};
+    ProfScope _ps(dt.prof, PK_ELEMWISE, s, 8.0 * dt.N * npoly * batch * (1 + level));
     k_rescale_lift<<<elem_grid(dt.N, npoly, batch), kElemThreads, 0, s>>>(g);
     LSB_CUDA(cudaGetLastError());
 }
@@ -340,6 +348,7 @@ void launch_bfv_rescale(const DeviceTables& dt, BatchPtr in, BatchPtr out, int n
                         int batch, cudaStream_t s) {
     if (batch <= 0) return;
     BfvRescaleArgs g{in, out, dt.N, npoly, level, qlinv_dev, dt.mods};
+    ProfScope _ps(dt.prof, PK_ELEMWISE, s, 8.0 * dt.N * npoly * batch * (2 * level + 1));
     k_bfv_rescale<<<elem_grid(dt.N, npoly, batch), kElemThreads, 0, s>>>(g);
     LSB_CUDA(cudaGetLastError());
 }
@@ -366,6 +375,7 @@ void launch_permute_ntt(const DeviceTables& dt, BatchPtr in, BatchPtr out, const
     if (batch <= 0 || map.n <= 0) return;
     PermArgs g{in, out, dt.N, dt.logN, index, 0, dt.mods, map};
     dim3 grid((dt.N + kElemThreads - 1) / kElemThreads, map.n, batch);
+    ProfScope _ps(dt.prof, PK_ELEMWISE, s, 8.0 * dt.N * map.n * batch * 2);
     k_permute_ntt<<<grid, kElemThreads, 0, s>>>(g);
     LSB_CUDA(cudaGetLastError());
 }
@@ -386,6 +396,7 @@ void launch_permute_coeff(const DeviceTables& dt, BatchPtr in, BatchPtr out, con
     if (batch <= 0 || map.n <= 0) return;
     PermArgs g{in, out, dt.N, dt.logN, nullptr, gal, dt.mods, map};
     dim3 grid((dt.N + kElemThreads - 1) / kElemThreads, map.n, batch);
+    ProfScope _ps(dt.prof, PK_ELEMWISE, s, 8.0 * dt.N * map.n * batch * 2);
     k_permute_coeff<<<grid, kElemThreads, 0, s>>>(g);
     LSB_CUDA(cudaGetLastError());
 }
@@ -406,6 +417,7 @@ __global__ void __launch_bounds__(kElemThreads) k_lift_ringt(const __grid_consta
 void launch_lift_ringt(const DeviceTables& dt, BatchPtr in, BatchPtr out, int nl, int batch, cudaStream_t s) {
     if (batch <= 0) return;
     LiftArgs g{in, out, dt.N, nl};
+    ProfScope _ps(dt.prof, PK_ELEMWISE, s, 8.0 * dt.N * batch * (1 + nl));
     k_lift_ringt<<<elem_grid(dt.N, 1, batch), kElemThreads, 0, s>>>(g);
     LSB_CUDA(cudaGetLastError());
 }
@@ -435,6 +447,7 @@ void launch_bfv_scale_up(const DeviceTables& dt, BatchPtr in, BatchPtr out, int 
     if (batch <= 0) return;
     ScaleUpArgs g{in, out, dt.N, nl, sc_dev, dt.mods};
     dim3 grid((dt.N + kElemThreads - 1) / kElemThreads, 1, batch);
+    ProfScope _ps(dt.prof, PK_ELEMWISE, s, 8.0 * dt.N * batch * (1 + nl));
     k_bfv_scale_up<<<grid, kElemThreads, 0, s>>>(g);
     LSB_CUDA(cudaGetLastError());
 }

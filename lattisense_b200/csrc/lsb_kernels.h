@@ -1,6 +1,7 @@
 // Kernel launchers of the B200 executor core (all asynchronous on the given stream).
 #pragma once
 #include "lsb_common.h"
+#include "lsb_prof.h"
 
 namespace lsb {
 
@@ -13,6 +14,7 @@ struct DeviceTables {
     const Tw* tw_fwd = nullptr;  // [nmod][N]  psi^bitrev(i) with Shoup companion
     const Tw* tw_inv = nullptr;  // [nmod][N]  psi^-bitrev(i)
     const ModConst* mods = nullptr;
+    Profiler* prof = nullptr;
 };
 
 // ---- NTT ----

@@ -235,6 +235,7 @@ void launch_ntt(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap&
     a.mods = dt.mods;
     a.map = map;
     const int sms = dt.sm_count;
+    ProfScope _ps(dt.prof, inverse ? PK_NTT_INV : PK_NTT_FWD, s, 16.0 * dt.N * a.total_rows, dt.logN > 14 ? 2 : 1);
 #define LSB_NTT_CASE1(L)                                  \
     case L:                                               \
         if (inverse) launch_single<L, true>(a, sms, s);   \

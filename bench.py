@@ -1,0 +1,304 @@
+#!/usr/bin/env python
+"""bench.py — BASELINE.json metric on its quoted configuration.
+
+Workload (BASELINE.json configs[1]): CKKS mult_relin + rescale, n = 16384, level 3 -> 2
+(parameter set frontend/parameter.json:95-114), a batch of 1024 ciphertexts per GPU.  One "step" =
+one pass of the hot path over the batch.  `value` = ciphertext ops/s with inputs resident in HBM;
+`e2e` = the same through the C ABI with HOST buffers (pinned H2D of both input batches and D2H of
+the result inside the timed region).  Inputs (2 GiB per step) are larger than L2, so no L2 flush
+is needed between iterations.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--impl ours|reference]
+
+Under torchrun (N > 1) every rank drives its own GPU with its own batch (weak scaling, no data-path
+collective: ciphertext batches are independent); time = max over ranks.
+`--impl reference` times the CPU path (oracle restatement of the reference's Lattigo path; the
+reference's own CPU library cannot be built here: Go + the lattigo submodule are absent) on the
+host cores for the same metric.
+"""
+import argparse
+import json
+import multiprocessing as mp
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import numpy as np  # noqa: E402
+
+METRIC = "ckks_mult_relin_rescale_ops_per_s"
+UNIT = "ciphertext ops/s"
+LEVEL = 3
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled during the timed region"""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5)
+                self.rows.append([x.strip() for x in out.stdout.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        self.stop_flag = True
+        self.join(timeout=6)
+        sm = sorted(int(r[0]) for r in self.rows if len(r) >= 6 and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) >= 6 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 6 and r[2 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU arm (oracle = restatement of the reference's Lattigo CPU path)
+# ---------------------------------------------------------------------------------------------
+_W = {}
+
+
+def _cpu_init():
+    import fhe_ref as R
+    o = R.Oracle(R.CKKS_N14)
+    rng = np.random.default_rng(os.getpid())
+    q, p = R.CKKS_N14.q, R.CKKS_N14.p
+    l = LEVEL + 1
+    mk = lambda mods, lead: np.stack([rng.integers(0, m, size=lead + (o.N,), dtype=np.uint64) for m in mods], axis=-2)
+    _W["o"] = o
+    _W["a"], _W["b"] = mk(q[:l], (2,)), mk(q[:l], (2,))
+    _W["rlk"] = np.ascontiguousarray(mk(q[:l] + p, (o.p.beta(LEVEL), 2)))
+
+
+def _cpu_work(n):
+    o = _W["o"]
+    t0 = time.perf_counter()
+    for _ in range(n):
+        o.rescale(o.relin(o.mult(_W["a"], _W["b"]), _W["rlk"]))
+    return time.perf_counter() - t0
+
+
+def cpu_ops_per_s(cores, ops_per_core):
+    """all cores, one oracle per process (the reference CPU runner uses min(32, hw) pool threads,
+    mega_ag_runners/cpu/cpu_wrapper.cpp:57)"""
+    import fhe_ref as R
+    R.build_oracle()
+    with mp.get_context("fork").Pool(cores, initializer=_cpu_init) as pool:
+        pool.map(_cpu_work, [1] * cores)  # warm-up
+        t0 = time.perf_counter()
+        pool.map(_cpu_work, [ops_per_core] * cores)
+        dt = time.perf_counter() - t0
+    return cores * ops_per_core / dt, dt
+
+
+def run_reference(args):
+    """--impl reference: the CPU path on the host cores, same metric/config; rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    cores = len(os.sched_getaffinity(0))
+    per_core = 40
+    steps_val = []
+    for _ in range(args.warmup):
+        cpu_ops_per_s(cores, 4)
+    t_all = 0.0
+    for _ in range(args.steps):
+        v, dt = cpu_ops_per_s(cores, per_core)
+        steps_val.append(v)
+        t_all += dt
+    value = float(np.mean(steps_val))
+    sample = "%d mult_relin_rescale ops per step (%d per core) of the %d-ciphertext batch" % (
+        cores * per_core, per_core, args.batch)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_all / max(args.steps, 1),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": "CKKS mult_relin+rescale n=16384 level 3->2 (BASELINE configs[1])",
+                   "batch_per_gpu": args.batch, "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "CPU baseline is the oracle restatement of the Lattigo path (Go toolchain + lattigo submodule absent)",
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import ctypes as C
+    import torch
+    import fhe_ref as R
+    import lattisense_b200 as L
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+    P = R.CKKS_N14
+    N, l, B = P.N, LEVEL + 1, args.batch
+    ctx = L.Context(P.scheme, P.logN, P.q, P.p, 0, device=local)
+    stream = torch.cuda.current_stream().cuda_stream
+    ctx.stream = stream
+    lib = L.lib()
+
+    def rand_limbs(lead, mods):
+        t = torch.empty(lead + (len(mods), N), dtype=torch.int64, device=dev)
+        for i, m in enumerate(mods):
+            t[..., i, :] = torch.randint(0, m, lead + (N,), dtype=torch.int64, device=dev)
+        return t
+
+    torch.manual_seed(1234 + rank)
+    a_dev = rand_limbs((B, 2), P.q[:l])
+    b_dev = rand_limbs((B, 2), P.q[:l])
+    rlk_dev = rand_limbs((P.beta(LEVEL), 2), P.q[:l] + P.p)
+    out_dev = torch.empty((B, 2, l - 1, N), dtype=torch.int64, device=dev)
+    a_host = torch.empty(a_dev.shape, dtype=torch.int64).pin_memory()
+    b_host = torch.empty(b_dev.shape, dtype=torch.int64).pin_memory()
+    out_host = torch.empty(out_dev.shape, dtype=torch.int64).pin_memory()
+    a_host.copy_(a_dev)
+    b_host.copy_(b_dev)
+    torch.cuda.synchronize()
+
+    def step_dev():
+        L._check(lib.lsb_mult_relin_rescale(ctx.h, LEVEL, a_dev.data_ptr(), b_dev.data_ptr(), rlk_dev.data_ptr(),
+                                            LEVEL, out_dev.data_ptr(), B, stream))
+
+    def step_e2e():
+        L._check(lib.lsb_upload(ctx.h, a_dev.data_ptr(), a_host.data_ptr(), a_host.numel(), stream))
+        L._check(lib.lsb_upload(ctx.h, b_dev.data_ptr(), b_host.data_ptr(), b_host.numel(), stream))
+        step_dev()
+        L._check(lib.lsb_download(ctx.h, out_host.data_ptr(), out_dev.data_ptr(), out_host.numel(), stream))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(max(args.warmup, 3)):
+        step_dev()
+    sampler = ClockSampler(local)
+    sampler.start()
+    n0 = ctx.launch_count()
+    ms = timed(step_dev, args.steps)
+    launches = ctx.launch_count() - n0
+    clocks = sampler.summary()
+    value = world * B * args.steps / (ms / 1e3)
+
+    # end-to-end through the C ABI with host buffers
+    step_e2e()
+    e2e_steps = max(1, min(args.steps, 5))
+    ms_e2e = timed(step_e2e, e2e_steps)
+    e2e_value = world * B * e2e_steps / (ms_e2e / 1e3)
+
+    # roofline pass: per-kernel-class CUDA events on the launching stream (one extra step, same inputs)
+    ctx.profile(True)
+    step_dev()
+    torch.cuda.synchronize()
+    kinds = ["ntt_fwd", "ntt_inv", "basis_ext", "ks_inner", "elementwise"]
+    prof = {k: ctx.profile_read(i) for i, k in enumerate(kinds)}
+    ctx.profile(False)
+    peak, peak_src = peaks()
+    tot_ms = sum(v[0] for v in prof.values())
+    ntt_ms = prof["ntt_fwd"][0] + prof["ntt_inv"][0]
+    ntt_bytes = prof["ntt_fwd"][2] + prof["ntt_inv"][2]
+    ntt_k = prof["ntt_fwd"][1] + prof["ntt_inv"][1]
+    achieved = ntt_bytes / (ntt_ms / 1e3) / 1e9 if ntt_ms > 0 else 0.0
+
+    # stand-alone NTT throughput: 8*B limb transforms in one launch, in place
+    mi = (C.c_int * l)(*range(l))
+    for _ in range(3):
+        L._check(lib.lsb_ntt(ctx.h, a_dev.data_ptr(), a_dev.data_ptr(), 2 * l, mi, l, 0, B, stream))
+    reps = 10
+    ms_ntt = timed(lambda: L._check(lib.lsb_ntt(ctx.h, a_dev.data_ptr(), a_dev.data_ptr(), 2 * l, mi, l, 0, B,
+                                                stream)), reps)
+    ntt_alone = 16.0 * N * 2 * l * B * reps / (ms_ntt / 1e3) / 1e9
+
+    if rank != 0:
+        return
+    cores = len(os.sched_getaffinity(0))
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        v, dt = cpu_ops_per_s(cores, 25)
+        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": "%d mult_relin_rescale ops (25 per core, %.1f s) of the same workload" % (25 * cores, dt)}
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": "CKKS mult_relin+rescale n=16384 level 3->2 (BASELINE configs[1])",
+                   "batch_per_gpu": B, "l2": "inputs (2 GiB/step) larger than L2, no flush needed",
+                   "parallelism": "batch-sharded x%d, no collective" % world},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": (a_host.numel() + b_host.numel()) * 8,
+                "d2h_bytes_per_step": out_host.numel() * 8, "ms_per_step": ms_e2e / e2e_steps,
+                "path": "C ABI lsb_upload + lsb_mult_relin_rescale + lsb_download, pinned host buffers"},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "kernel": "k_ntt_single<14> (fwd+inv, in-step average)",
+                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "peak_source": peak_src, "launches": ntt_k, "ms_per_launch": ntt_ms / max(ntt_k, 1),
+                     "share_of_step": ntt_ms / tot_ms if tot_ms else None,
+                     "standalone_ntt_gbs": ntt_alone, "standalone_frac": ntt_alone / peak},
+        "kernel_ms_per_step": {k: v[0] for k, v in prof.items()},
+        "cpu_baseline": cpu,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--batch", type=int, default=1024)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

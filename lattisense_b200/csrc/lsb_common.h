@@ -59,6 +59,7 @@ struct RowMap {
 // Per-modulus constants resident on the device.
 struct ModConst {
     u64 q;
+    u64 qinv64;  // floor((2^64-1)/q)
     BarrettQ bq;
     Tw ninv;    // N^-1
     Tw w_ninv;  // psi^-1_br[1] * N^-1

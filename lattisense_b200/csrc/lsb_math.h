@@ -96,6 +96,20 @@ LSB_HD void ct_bfly(u64& x, u64& y, Tw t, u64 q, u64 q2) {
     x = X + T;
     y = X - T + q2;
 }
+// Same without the range correction on x: every stage adds at most 2q to the bound, so a whole
+// logN-stage transform stays below (2 logN + 1) q < 2^64 when q < 2^58 (kLazyLimit).
+LSB_HD void ct_bfly_nocorr(u64& x, u64& y, Tw t, u64 q, u64 q2) {
+    u64 T = mul_shoup_lazy(y, t, q);
+    y = x - T + q2;
+    x = x + T;
+}
+constexpr u64 kLazyLimit = 1ull << 58;
+// v < 2^64 -> v mod q, qinv64 = floor((2^64-1)/q)
+LSB_HD u64 reduce_full(u64 v, u64 q, u64 qinv64) {
+    u64 r = v - umulhi(v, qinv64) * q;  // [0, 2q)
+    return csub(r, q);
+}
+
 // Inverse (Gentleman-Sande, lazy) butterfly: x,y in [0,2q) -> outputs in [0,2q).
 LSB_HD void gs_bfly(u64& x, u64& y, Tw t, u64 q, u64 q2) {
     u64 s = csub(x + y, q2);

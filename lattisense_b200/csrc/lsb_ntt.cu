@@ -9,6 +9,7 @@
 //  * N  = 2^15, 2^16: column pass (stages [0, logN-8) on 16-column strided tiles, 128-byte
 //    segments) + row pass (last 8 stages on 4096-word contiguous tiles).
 #include <type_traits>
+#include <cstdlib>
 #include "lsb_kernels.h"
 #include "lsb_ntt_core.h"
 
@@ -53,15 +54,23 @@ __global__ void __launch_bounds__(SingleCfg<LOGN>::NT, 1) k_ntt_single(const __g
         const Tw* tw = a.tw + (size_t)mod * N;
         const u64 q = a.mods[mod].q;
         if (!INV) {
+            const u64 qinv64 = a.mods[mod].qinv64;
+            const bool lazy = q < kLazyLimit;  // CTA-uniform
             static_for<0, P.nrounds>([&](auto ic) {
                 constexpr int i = decltype(ic)::value;
                 constexpr int lr = P.rounds[i].lr;
                 constexpr int loggc = plan_loggc(P, i);
                 constexpr int SRC = i == 0 ? IO_GLOBAL : IO_SMEM;
                 constexpr bool FINAL = i == P.nrounds - 1;
-                for (int g = tid; g < (N >> lr); g += NT)
-                    fwd_round<lr, SRC, IO_SMEM, FINAL, loggc == 0>(sm, src, nullptr, tg, tw, g, loggc, P.rounds[i].v, 1u,
-                                                                  q);
+                if (lazy) {
+                    for (int g = tid; g < (N >> lr); g += NT)
+                        fwd_round<lr, SRC, IO_SMEM, FINAL, loggc == 0, true>(sm, src, nullptr, tg, tw, g, loggc,
+                                                                            P.rounds[i].v, 1u, q, qinv64);
+                } else {
+                    for (int g = tid; g < (N >> lr); g += NT)
+                        fwd_round<lr, SRC, IO_SMEM, FINAL, loggc == 0, false>(sm, src, nullptr, tg, tw, g, loggc,
+                                                                             P.rounds[i].v, 1u, q);
+                }
                 __syncthreads();
             });
             for (int c = tid; c < N / 2; c += NT)
@@ -119,9 +128,12 @@ __global__ void __launch_bounds__((1 << (LOGN - kRowLS + kColLC)) / 16) k_ntt_co
             constexpr int SRC = j == 0 ? IO_GLOBAL : IO_SMEM;
             constexpr int DST = j == P.nrounds - 1 ? IO_GLOBAL : IO_SMEM;
             for (int g = tid; g < (T >> lr); g += NT) {
-                if (!INV)
-                    fwd_round<lr, SRC, DST, false, false>(sm, src, dst, tg, tw, g, loggc, P.rounds[i].v, 1u, q);
-                else
+                if (!INV) {
+                    if (q < kLazyLimit)
+                        fwd_round<lr, SRC, DST, false, false, true>(sm, src, dst, tg, tw, g, loggc, P.rounds[i].v, 1u, q);
+                    else
+                        fwd_round<lr, SRC, DST, false, false, false>(sm, src, dst, tg, tw, g, loggc, P.rounds[i].v, 1u, q);
+                } else
                     inv_round<lr, SRC, DST, i == 0, false>(sm, src, dst, tg, tw, g, loggc, P.rounds[i].v, 1u, q, ninv,
                                                            w_ninv);
             }
@@ -155,9 +167,16 @@ __global__ void __launch_bounds__(256) k_ntt_rows(const __grid_constant__ NttArg
         const u32 twbase = (1u << LA) + (u32)(tb * kRowSub + st);
         u64* smt = sm + st * S;
         if (!INV) {
-            fwd_round<4, IO_GLOBAL, IO_SMEM, false, false>(smt, src + st * S, nullptr, tg, tw, g, 4, 0, twbase, q);
-            __syncthreads();
-            fwd_round<4, IO_SMEM, IO_SMEM, true, true>(smt, nullptr, nullptr, tg, tw, g, 0, 4, twbase, q);
+            const u64 qinv64 = a.mods[mod].qinv64;
+            if (q < kLazyLimit) {
+                fwd_round<4, IO_GLOBAL, IO_SMEM, false, false, true>(smt, src + st * S, nullptr, tg, tw, g, 4, 0, twbase, q);
+                __syncthreads();
+                fwd_round<4, IO_SMEM, IO_SMEM, true, true, true>(smt, nullptr, nullptr, tg, tw, g, 0, 4, twbase, q, qinv64);
+            } else {
+                fwd_round<4, IO_GLOBAL, IO_SMEM, false, false, false>(smt, src + st * S, nullptr, tg, tw, g, 4, 0, twbase, q);
+                __syncthreads();
+                fwd_round<4, IO_SMEM, IO_SMEM, true, true, false>(smt, nullptr, nullptr, tg, tw, g, 0, 4, twbase, q);
+            }
             __syncthreads();
             for (int c = tid; c < T / 2; c += NT)
                 reinterpret_cast<W2*>(dst)[c] = *reinterpret_cast<const W2*>(&sm[swz(2 * c)]);
@@ -246,6 +265,15 @@ void launch_ntt(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap&
         if (inverse) launch_two_pass<L, true>(a, sms, s); \
         else launch_two_pass<L, false>(a, sms, s);        \
         break;
+    static const bool two14 = [] {
+        const char* e = getenv("LSB_NTT_TWOPASS");
+        return e && atoi(e) != 0;
+    }();
+    if (dt.logN == 14 && two14) {
+        if (inverse) launch_two_pass<14, true>(a, sms, s);
+        else launch_two_pass<14, false>(a, sms, s);
+        return;
+    }
     switch (dt.logN) {
         LSB_NTT_CASE1(12)
         LSB_NTT_CASE1(13)

@@ -40,9 +40,10 @@ struct __attribute__((aligned(16))) W2 {
 
 // One forward round.  SRC/DST select shared memory (swizzled) or global memory (through gaddr).
 // FINAL: reduce outputs to [0,q) (last round of the whole transform).
-template <int LR, int SRC, int DST, bool FINAL, bool VEC>
+// LAZY: no per-butterfly range correction (q < kLazyLimit); FINAL then reduces with qinv64.
+template <int LR, int SRC, int DST, bool FINAL, bool VEC, bool LAZY = false>
 LSB_HD void fwd_round(u64* sm, const u64* gsrc, u64* gdst, const TileGeom tg, const Tw* __restrict__ tw, int g,
-                      int logGC, int v, u32 twbase, u64 q) {
+                      int logGC, int v, u32 twbase, u64 q, u64 qinv64 = 0) {
     constexpr int R = 1 << LR;
     const u64 q2 = q << 1;
     const int hi = g >> logGC;
@@ -70,12 +71,15 @@ LSB_HD void fwd_round(u64* sm, const u64* gsrc, u64* gdst, const TileGeom tg, co
         for (int kg = 0; kg < (1 << r); kg++) {
             const Tw t = tw[(tbase << r) | (u32)kg];
 #pragma unroll
-            for (int i = 0; i < hk; i++) ct_bfly(x[kg * 2 * hk + i], x[kg * 2 * hk + i + hk], t, q, q2);
+            for (int i = 0; i < hk; i++) {
+                if (LAZY) ct_bfly_nocorr(x[kg * 2 * hk + i], x[kg * 2 * hk + i + hk], t, q, q2);
+                else ct_bfly(x[kg * 2 * hk + i], x[kg * 2 * hk + i + hk], t, q, q2);
+            }
         }
     }
     if (FINAL) {
 #pragma unroll
-        for (int k = 0; k < R; k++) x[k] = csub(csub(x[k], q2), q);
+        for (int k = 0; k < R; k++) x[k] = LAZY ? reduce_full(x[k], q, qinv64) : csub(csub(x[k], q2), q);
     }
     if (DST == IO_SMEM && VEC) {
 #pragma unroll

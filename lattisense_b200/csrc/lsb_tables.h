@@ -27,6 +27,7 @@ inline void build_ntt_tables(u64 qq, int logN, Tw* f, Tw* iv, ModConst* mc) {
     }
     const u64 ninv = invmod(N % qq, qq);
     mc->q = qq;
+    mc->qinv64 = ~0ull / qq;
     mc->bq = make_barrett(qq);
     mc->ninv = make_tw(ninv, qq);
     mc->w_ninv = make_tw(mulmod(iv[1].w, ninv, qq), qq);

@@ -14,7 +14,9 @@ static void round_dyn(int lr, int src, int dst, bool fin, bool vec, u64* sm, con
                       const Tw* tw, int g, int loggc, int v, u32 twbase, const ModConst& mc) {
 #define CASE(LR, S, D, F, V)                                                                                   \
     if (lr == LR && src == S && dst == D && fin == F && vec == V) {                                            \
-        if (!INV) fwd_round<LR, S, D, F, V>(sm, gsrc, gdst, tg, tw, g, loggc, v, twbase, mc.q);                \
+        if (!INV && mc.q < kLazyLimit)                                                                         \
+            fwd_round<LR, S, D, F, V, true>(sm, gsrc, gdst, tg, tw, g, loggc, v, twbase, mc.q, mc.qinv64);     \
+        else if (!INV) fwd_round<LR, S, D, F, V, false>(sm, gsrc, gdst, tg, tw, g, loggc, v, twbase, mc.q);    \
         else inv_round<LR, S, D, F, V>(sm, gsrc, gdst, tg, tw, g, loggc, v, twbase, mc.q, mc.ninv, mc.w_ninv); \
         return;                                                                                                \
     }

@@ -1,0 +1,135 @@
+/*
+ * lattisense_gpu_runner.h — the drop-in boundary of libgpu_mega_ag_runner.so.
+ *
+ * These are the entry points the reference's SDK and plug-ins bind for the GPU path
+ * (paths relative to cipherflow-fhe/lattisense @ 88bf833):
+ *   - cxx_sdk_v2/cxx_fhe_task_gpu.cpp:32-117 (FheTaskGpu) links them directly,
+ *   - plug-in/lattigo/acc/gpu_runner.go:6 (cgo, -lgpu_mega_ag_runner),
+ *   - plug-in/SEAL/acc/CMakeLists.txt:14.
+ * Prototypes, argument meaning and error behaviour follow mega_ag_runners/wrapper.h:67-85 and the
+ * implementation in mega_ag_runners/gpu/gpu_wrapper.cu:481-530; the argument and ciphertext/key
+ * structs are byte-compatible restatements of mega_ag_runners/c_argument.h:24-46 and
+ * abi/c_types.h:26-60.  The `void*` executor parameters are pointers to C++ `ExecutorFunc`
+ * objects (see lattisense_mega_ag.hpp) which are copied during the call, exactly as in the reference.
+ *
+ * Errors: like the reference (gpu_abi_bridge_executors.h:51-55, gpu_wrapper.cu:468) failures inside
+ * create/bind/run surface as C++ exceptions (std::runtime_error); run_fhe_gpu_task additionally
+ * returns non-zero when a node failed (the SDK turns that into a throw, cxx_fhe_task_gpu.cpp:106-108).
+ * There is no CPU fallback: without a CUDA device run_fhe_gpu_task fails.
+ */
+#ifndef LATTISENSE_GPU_RUNNER_H
+#define LATTISENSE_GPU_RUNNER_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- mega_ag_runners/c_argument.h:24-46 ---- */
+#ifndef LATTISENSE_C_ARGUMENT_DEFINED
+#define LATTISENSE_C_ARGUMENT_DEFINED
+typedef enum {
+    TYPE_PLAINTEXT,
+    TYPE_CIPHERTEXT,
+    TYPE_RELIN_KEY,
+    TYPE_GALOIS_KEY,
+    TYPE_SWITCH_KEY,
+    TYPE_CUSTOM,
+} DataType;
+
+typedef enum {
+    ALGO_BFV,
+    ALGO_CKKS,
+} Algo;
+
+typedef struct {
+    const char* id; /* argument name from task_signature.json */
+    DataType type;
+    void* data; /* void*[size]: opaque frontend handles, only ever dereferenced by the bound executors */
+    int level;
+    int size;
+} CArgument;
+#endif
+
+/* ---- abi/c_types.h:26-60: wire layout of ciphertexts, plaintexts and keys ---- */
+#ifndef LATTISENSE_C_TYPES_DEFINED
+#define LATTISENSE_C_TYPES_DEFINED
+typedef struct {
+    int n;          /* ring degree N */
+    uint64_t* data; /* N residues in [0, q_i), malloc'd per limb (abi/c_structs.c:23-26) */
+} CComponent;
+
+typedef struct {
+    int n_component; /* level+1 limbs (keys: level+1 Q limbs then k P limbs) */
+    CComponent* components;
+} CPolynomial;
+
+typedef struct {
+    int level;
+    CPolynomial poly;
+} CPlaintext;
+
+typedef struct {
+    int level;
+    int degree; /* polys = degree+1 */
+    CPolynomial* polys;
+} CCiphertext;
+
+typedef CCiphertext CPublicKey;
+
+typedef struct {
+    int n_public_key; /* beta = ceil((level+1)/k) digits, each a degree-1 "ciphertext" over Q u P */
+    CPublicKey* public_keys;
+} CKeySwitchKey;
+
+typedef CKeySwitchKey CRelinKey;
+
+typedef struct {
+    int n_key_switch_key;
+    uint64_t* galois_elements;
+    CKeySwitchKey* key_switch_keys;
+} CGaloisKey;
+#endif
+
+/* ---- abi/c_structs.h:22-44, abi/c_structs.c:23-98: allocation helpers (same malloc-per-limb ownership) ---- */
+void alloc_component(CComponent* component, int n);
+void alloc_plaintext(CPlaintext* pt, int level, int n);
+void alloc_ciphertext(CCiphertext* ct, int degree, int level, int n);
+void alloc_relin_key(CRelinKey* rlk, int n_public_key, int level, int n);
+void set_galois_key_steps(CGaloisKey* glk, uint64_t* galois_elements, int n_galois_elements);
+void free_plaintext(CPlaintext* pt);
+void free_ciphertext(CCiphertext* ct);
+void free_relin_key(CRelinKey* rlk);
+void free_galois_key(CGaloisKey* gk);
+
+/* ---- mega_ag_runners/wrapper.h:26-42, 67-85 ---- */
+typedef struct fhe_task_handle_st* fhe_task_handle;
+/* invoked from worker threads, (completed, total) compute nodes */
+typedef void (*progress_callback_t)(int completed, int total, void* user_data);
+
+/* Loads <project_path>/mega_ag.json (gpu_wrapper.cu:412-431). */
+fhe_task_handle create_fhe_gpu_task(const char* project_path);
+void release_fhe_gpu_task(fhe_task_handle handle);
+/* abi_export_executor / abi_import_executor: ExecutorFunc* (gpu_wrapper.cu:492-497). */
+void bind_gpu_task_abi_bridge_executors(fhe_task_handle handle, void* abi_export_executor, void* abi_import_executor);
+/* executors[i]: ExecutorFunc* for custom node type custom_types[i] (gpu_wrapper.cu:499-510). */
+void bind_gpu_task_custom_executors(fhe_task_handle handle, const char** custom_types, void** executors,
+                                    uint64_t n_executors);
+/* Runs the task graph on GPU `gpu_device`; synchronous; 0 on success (gpu_wrapper.cu:512-529).
+ * Inputs are flattened in mega_ag.inputs order (keys after data: rlk, glk, swk_dts, swk_std;
+ * cxx_sdk_v2/cxx_argument.h:178-260), outputs map positionally onto mega_ag.outputs. */
+int run_fhe_gpu_task(fhe_task_handle handle, CArgument* input_args, uint64_t n_in_args, CArgument* output_args,
+                     uint64_t n_out_args, progress_callback_t progress_cb, void* user_data, int gpu_device);
+
+/* ---- extensions of this implementation (not in the reference; optional for callers) ---- */
+/* Devices used by the NEXT run of this task: independent components of the DAG are sharded over
+ * devices[0..n).  Default: the single `gpu_device` passed to run_fhe_gpu_task. */
+void lsb_gpu_task_set_devices(fhe_task_handle handle, const int* devices, int n_devices);
+/* Statistics of the last run: kernel launches, batched launch groups, nodes fused away. */
+void lsb_gpu_task_last_stats(fhe_task_handle handle, long long* kernel_launches, long long* batched_groups,
+                             long long* fused_nodes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LATTISENSE_GPU_RUNNER_H */

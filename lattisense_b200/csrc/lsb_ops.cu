@@ -433,6 +433,50 @@ void op_mul_plain_ringt(OpEnv& e, int level, int npoly, BatchPtr ct, BatchPtr pt
     }
 }
 
+// sum_i ct_i x pt_i (+ partial sum): bind_gpu_cmp_sum / bind_gpu_cmpac_sum (mega_ag_executors_gpu.cu:294-408).
+// Products are accumulated in the NTT domain; a BFV result takes a single INTT at the end.
+void op_mac(OpEnv& e, int level, int nterms, const BatchPtr* cts, const BatchPtr* pts, bool ringt, bool has_acc,
+            BatchPtr acc_in, BatchPtr out, int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    Context& c = e.c;
+    const int l = level + 1;
+    const bool bfv = c.scheme == SCHEME_BFV;
+    LSB_CHECK(nterms >= 1, "lsb: mac needs at least one term");
+    // [acc 2l | ptm l | t 2l]
+    const size_t item = (size_t)(2 * l + l + (bfv ? 2 * l : 0)) * c.N;
+    const int chunk = pick_chunk(e, item, batch, 2 * l);
+    u64* scratch = e.ws.reserve(item * chunk, e.s);
+    for (int b0 = 0; b0 < batch; b0 += chunk) {
+        const int nb = std::min(chunk, batch - b0);
+        BatchPtr acc = bp_strided(scratch, item);
+        BatchPtr ptm = bp_strided(scratch + (size_t)2 * l * c.N, item);
+        BatchPtr t = bp_strided(scratch + (size_t)3 * l * c.N, item);
+        // a CKKS sum without partial input accumulates straight into the output
+        BatchPtr dst = (!bfv && !has_acc) ? adv(out, b0) : acc;
+        for (int i = 0; i < nterms; i++) {
+            BatchPtr pt = adv(pts[i], b0);
+            if (ringt) {
+                launch_lift_ringt(c.dt, pt, ptm, l, nb, e.s);
+                launch_ntt(c.dt, ptm, ptm, rowmap_seq(l, 0, 0, 0, l), nb, false, e.s);
+                pt = ptm;
+            }
+            BatchPtr ct = adv(cts[i], b0);
+            if (bfv) {
+                launch_ntt(c.dt, ct, t, rowmap_seq(2 * l, 0, 0, 0, l), nb, false, e.s);
+                ct = t;
+            }
+            launch_mul_plain(c.dt, ct, pt, dst, 2, l, i > 0, nb, e.s);
+        }
+        if (bfv) {
+            launch_ntt(c.dt, acc, acc, rowmap_seq(2 * l, 0, 0, 0, l), nb, true, e.s);
+            if (has_acc) launch_binary(c.dt, OP_ADD, acc, adv(acc_in, b0), adv(out, b0), rowmap_seq(2 * l, 0, 0, 0, l), 2 * l, nb, e.s);
+            else launch_binary(c.dt, OP_ADD, acc, acc, adv(out, b0), rowmap_seq(2 * l, 0, 0, 0, l), 0, nb, e.s);
+        } else if (has_acc) {
+            launch_binary(c.dt, OP_ADD, acc, adv(acc_in, b0), adv(out, b0), rowmap_seq(2 * l, 0, 0, 0, l), 2 * l, nb, e.s);
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // fused chains
 // ---------------------------------------------------------------------------------------------

@@ -39,6 +39,11 @@ void op_mul_plain(OpEnv& e, int level, int npoly, BatchPtr ct, BatchPtr pt, Batc
 // ct x pt_ringt
 void op_mul_plain_ringt(OpEnv& e, int level, int npoly, BatchPtr ct, BatchPtr pt, BatchPtr out, int batch);
 
+// bind_gpu_cmp_sum / bind_gpu_cmpac_sum (:294-408): sum_i ct_i x pt_i (+ acc_in); pts are pt_ringt ([1][N] mod t)
+// when `ringt`, NTT-domain [level+1][N] plaintexts otherwise
+void op_mac(OpEnv& e, int level, int nterms, const BatchPtr* cts, const BatchPtr* pts, bool ringt, bool has_acc,
+            BatchPtr acc_in, BatchPtr out, int batch);
+
 // fused paths used by the runner's pattern matcher and by the benchmark
 void op_mult_relin(OpEnv& e, int level, BatchPtr a, BatchPtr b, const u64* rlk, int key_level, BatchPtr out2,
                    int batch);

@@ -1,0 +1,198 @@
+"""Generates tests/golden/graphs/<case>/{mega_ag.json,task_signature.json} with the REFERENCE's own
+graph compiler (frontend/custom_task.py, imported from /root/reference — it runs in the build
+container but does not travel to the GPU box, hence the committed fixtures).
+
+    PYTHONPATH=/root/reference python tests/golden/make_graphs.py
+
+Cases mirror the reference's GPU test list (unittests/test_gpu_bfv.py, test_gpu_ckks.py: N_OP
+independent copies per graph) and the BASELINE.json configs.  Parameter sets: the reference's test
+fixtures (unittests/fixture.hpp:74-79, 96-103) at n=8192 and the defaults at n=16384.
+"""
+import os
+import shutil
+import sys
+
+REF = os.environ.get("LATTISENSE_REFERENCE", "/root/reference")
+sys.path.insert(0, REF)
+from frontend.custom_task import *  # noqa: E402,F401,F403
+
+OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "graphs")
+N_OP = 4
+
+BFV8K = dict(n=8192, q=[0x3FFFFFFFEF8001, 0x4000000011C001, 0x40000000120001], p=[0x7FFFFFFFFB4001], t=65537)
+CKKS8K = dict(n=8192, q=[0x1FFFEC001, 0x3FFF4001, 0x3FFE8001, 0x40020001, 0x40038001, 0x3FFC0001], p=[0x800004001],
+              scale=float(1 << 30))
+
+
+def bfv8k():
+    return BfvParam.create_custom_param(**BFV8K)
+
+
+def ckks8k():
+    return CkksParam.create_custom_param(n=CKKS8K["n"], q=list(CKKS8K["q"]), p=list(CKKS8K["p"]), scale=CKKS8K["scale"])
+
+
+def emit(case, ins, outs, offline=()):
+    d = os.path.join(OUT, case)
+    shutil.rmtree(d, ignore_errors=True)
+    process_custom_task(input_args=ins, offline_input_args=list(offline), output_args=outs,
+                        output_instruction_path=d, fpga_acc=False)
+    for f in os.listdir(d):
+        if f not in ("mega_ag.json", "task_signature.json"):
+            p = os.path.join(d, f)
+            shutil.rmtree(p) if os.path.isdir(p) else os.remove(p)
+    print("wrote", case)
+
+
+def binary_case(case, param, Ct, Other, fn, lv, other_level=True):
+    set_fhe_param(param)
+    xs = [Ct(f"x_{i}", level=lv) for i in range(N_OP)]
+    ys = [Other(f"y_{i}", level=lv) if other_level else Other(f"y_{i}") for i in range(N_OP)]
+    zs = [fn(xs[i], ys[i], f"z_{i}") for i in range(N_OP)]
+    emit(case, [Argument("in_x_list", xs), Argument("in_y_list", ys)], [Argument("out_z_list", zs)])
+
+
+def gen_scheme(tag, mkparam, Ct, Pt, PtRingt, PtMul, lv, n_sp):
+    binary_case(f"{tag}_cap", mkparam(), Ct, Pt, add, lv)
+    binary_case(f"{tag}_cac", mkparam(), Ct, Ct, add, lv)
+    binary_case(f"{tag}_csp", mkparam(), Ct, Pt, sub, lv)
+    binary_case(f"{tag}_csc", mkparam(), Ct, Ct, sub, lv)
+    binary_case(f"{tag}_cmp_ringt", mkparam(), Ct, PtRingt, mult, lv, other_level=False)
+    binary_case(f"{tag}_cmp", mkparam(), Ct, PtMul, mult, lv)
+    binary_case(f"{tag}_cmc", mkparam(), Ct, Ct, mult, lv)
+    binary_case(f"{tag}_cmc_relin", mkparam(), Ct, Ct, mult_relin, lv)
+    if tag.startswith("bfv"):
+        binary_case(f"{tag}_cap_ringt", mkparam(), Ct, PtRingt, add, lv, other_level=False)
+        binary_case(f"{tag}_csp_ringt", mkparam(), Ct, PtRingt, sub, lv, other_level=False)
+
+    set_fhe_param(mkparam())
+    xs = [Ct(f"x_{i}", level=lv) for i in range(N_OP)]
+    zs = [neg(xs[i], f"z_{i}") for i in range(N_OP)]
+    emit(f"{tag}_cneg", [Argument("in_x_list", xs)], [Argument("out_z_list", zs)])
+
+    set_fhe_param(mkparam())
+    xs = [Ct(f"x_{i}", level=lv) for i in range(N_OP)]
+    ys = [Ct(f"y_{i}", level=lv) for i in range(N_OP)]
+    zs = [rescale(mult_relin(xs[i], ys[i]), f"z_{i}") for i in range(N_OP)]
+    emit(f"{tag}_cmc_relin_rescale", [Argument("in_x_list", xs), Argument("in_y_list", ys)], [Argument("out_z_list", zs)])
+
+    set_fhe_param(mkparam())
+    xs = [Ct(f"x_{i}", level=lv) for i in range(N_OP)]
+    zs = [rescale(mult_relin(xs[i], xs[i]), f"z_{i}") for i in range(N_OP)]
+    emit(f"{tag}_csqr_relin_rescale", [Argument("in_x_list", xs)], [Argument("out_z_list", zs)])
+
+    set_fhe_param(mkparam())
+    xs = [Ct(f"x_{i}", level=lv) for i in range(N_OP)]
+    zs = [rescale(xs[i], f"z_{i}") for i in range(N_OP)]
+    emit(f"{tag}_rescale", [Argument("in_x_list", xs)], [Argument("out_z_list", zs)])
+
+    set_fhe_param(mkparam())
+    xs = [Ct(f"x_{i}", level=lv) for i in range(N_OP)]
+    steps = [1, 2, 3, 5]
+    ys = [rotate_cols(xs[i], steps) for i in range(N_OP)]
+    emit(f"{tag}_rotate_col", [Argument("in_x_list", xs)], [Argument("out_y_list", ys)])
+
+    set_fhe_param(mkparam())
+    xs = [Ct(f"x_{i}", level=lv) for i in range(N_OP)]
+    steps = [-900, 20, 400, 2000, 3009] if tag.startswith("bfv") else [-500, 20, 200, 2000, 4000]
+    ys = [advanced_rotate_cols(xs[i], steps) for i in range(N_OP)]
+    emit(f"{tag}_advanced_rotate_col", [Argument("in_x_list", xs)], [Argument("out_y_list", ys)])
+
+    set_fhe_param(mkparam())
+    xs = [Ct(f"x_{i}", level=lv) for i in range(N_OP)]
+    ys = [rotate_rows(xs[i], f"y_{i}") for i in range(N_OP)]
+    emit(f"{tag}_rotate_row", [Argument("in_x_list", xs)], [Argument("out_y_list", ys)])
+
+    # ct x pt_ringt multiply-accumulate (cmp_sum / cmpac_sum nodes)
+    set_fhe_param(mkparam())
+    m = 20
+    xs = [Ct(f"x_{i}", level=lv) for i in range(m)]
+    ys = [PtRingt(f"y_{i}") for i in range(m)]
+    z = ct_pt_mult_accumulate(xs, ys)
+    emit(f"{tag}_ct_pt_ringt_mac", [Argument("in_x_list", xs), Argument("in_y_list", ys)], [Argument("out_z", z)])
+
+    # ((x*y relin) rotated by 1) + x : mult -> relin -> rotate -> add chain
+    set_fhe_param(mkparam())
+    xs = [Ct(f"x_{i}", level=lv) for i in range(N_OP)]
+    ys = [Ct(f"y_{i}", level=lv) for i in range(N_OP)]
+    zs = []
+    for i in range(N_OP):
+        w = mult_relin(xs[i], ys[i])
+        r = rotate_cols(w, 1)[0]
+        zs.append(add(r, xs[i], f"z_{i}"))
+    emit(f"{tag}_ctc_rotate_cac", [Argument("in_x_list", xs), Argument("in_y_list", ys)], [Argument("out_z_list", zs)])
+
+    # a custom (CPU) node in the middle of the graph: x*y -> custom -> + x
+    set_fhe_param(mkparam())
+    x, y = Ct("x", level=lv), Ct("y", level=lv)
+    w = mult_relin(x, y)
+    c = Ct("c", level=lv)
+    custom_compute([w], c, "passthrough", {"note": "identity on the host", "k": 3})
+    z = add(c, x, "z")
+    emit(f"{tag}_custom_in_middle", [Argument("x", x), Argument("y", y)], [Argument("z", z)])
+
+
+def gen_ckks_extra(tag, mkparam, lv):
+    set_fhe_param(mkparam())
+    xs = [CkksCiphertextNode(f"x_{i}", level=lv) for i in range(N_OP)]
+    zs = [drop_level(xs[i], 2, f"z_{i}") for i in range(N_OP)]
+    emit(f"{tag}_drop_level", [Argument("in_x_list", xs)], [Argument("out_z_list", zs)])
+
+
+def gen_configs():
+    # cfg1: BFV mult_relin n=16384 t=65537 level 2 (examples/bfv_mult_cpu)
+    set_fhe_param(BfvParam.create_default_param(n=16384))
+    x, y = BfvCiphertextNode("x", level=2), BfvCiphertextNode("y", level=2)
+    z = mult_relin(x, y, "z")
+    emit("cfg1_bfv_mult", [Argument("x", x), Argument("y", y)], [Argument("z", z)])
+
+    # cfg2 (reduced copy count; bench.py replicates the node pattern to 1024): CKKS mult_relin + rescale
+    set_fhe_param(CkksParam.create_default_param(n=16384))
+    xs = [CkksCiphertextNode(f"x_{i}", level=3) for i in range(8)]
+    ys = [CkksCiphertextNode(f"y_{i}", level=3) for i in range(8)]
+    zs = [rescale(mult_relin(xs[i], ys[i]), f"z_{i}") for i in range(8)]
+    emit("cfg2_ckks_mult_x8", [Argument("in_x_list", xs), Argument("in_y_list", ys)], [Argument("out_z_list", zs)])
+
+    # cfg3: BFV degree-7 polynomial (examples/bfv_poly_7_cpu/bfv_poly_7_cpu.py:31-53)
+    set_fhe_param(BfvParam.create_default_param(n=16384))
+    level = 4
+    x = BfvCiphertextNode("x", level)
+    a = [BfvPlaintextMulNode(f"a_{i}", level - 3) for i in range(1, 8)]
+    a0 = BfvPlaintextNode("a_0", level - 3)
+    x2 = rescale(mult_relin(x, x))
+    x3 = rescale(mult_relin(x2, rescale(x)))
+    x4 = rescale(mult_relin(x2, x2))
+    x2r = rescale(x2)
+    x5 = rescale(mult_relin(x3, x2r))
+    x6 = rescale(mult_relin(x3, x3))
+    x7 = rescale(mult_relin(x3, x4))
+    pw = [rescale(rescale(rescale(x))), rescale(rescale(x2)), rescale(x3), rescale(x4), x5, x6, x7]
+    acc = None
+    for i in range(7):
+        term = mult(pw[i], a[i])
+        acc = term if acc is None else add(acc, term)
+    yv = add(acc, a0, "y")
+    emit("cfg3_bfv_poly7", [Argument("x", x), Argument("a", a), Argument("a_0", a0)], [Argument("y", yv)])
+
+    # cfg4: CKKS logistic-regression inference (examples/ckks_logistic_regression_cpu/...py:26-59), n=16384 as shipped
+    set_fhe_param(CkksParam.create_default_param(n=16384))
+    level = 3
+    xe = CkksCiphertextNode("x", level)
+    w = CkksPlaintextRingtNode("w")
+    b = CkksPlaintextNode("b", level - 1)
+    s = rescale(mult(xe, w))
+    for st in (16, 8, 4, 2, 1):
+        s = add(s, rotate_cols(s, st)[0])
+    s = add(s, b)
+    half = CkksPlaintextRingtNode("half")
+    o = rescale(mult(s, half), "out")
+    emit("cfg4_ckks_logreg", [Argument("x", xe), Argument("w", w), Argument("b", b), Argument("half", half)],
+         [Argument("out", o)])
+
+
+if __name__ == "__main__":
+    os.makedirs(OUT, exist_ok=True)
+    gen_scheme("bfv8k", bfv8k, BfvCiphertextNode, BfvPlaintextNode, BfvPlaintextRingtNode, BfvPlaintextMulNode, 2, 1)
+    gen_scheme("ckks8k", ckks8k, CkksCiphertextNode, CkksPlaintextNode, CkksPlaintextRingtNode, CkksPlaintextMulNode, 4, 1)
+    gen_ckks_extra("ckks8k", ckks8k, 4)
+    gen_configs()

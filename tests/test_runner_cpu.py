@@ -1,0 +1,113 @@
+"""Host-side tests of the mega_ag runner boundary (no GPU): exported symbols, graph loading with ABI-bridge
+insertion (mega_ag_runners/mega_ag.cpp:388-544), chain fusion, component sharding, error reporting."""
+import ctypes as C
+import json
+import os
+import re
+
+import pytest
+
+import graph_eval as GE
+
+ROOT = GE.ROOT
+
+
+def _declared(header):
+    txt = open(os.path.join(ROOT, "include", header)).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    txt = re.sub(r"//[^\n]*", "", txt)
+    txt = re.sub(r"typedef[^;{]*\([^;]*;", "", txt)  # function-pointer typedefs
+    names = re.findall(r"\b([a-z_][a-z0-9_]*)\s*\([^;{]*\)\s*;", txt)
+    return sorted({n for n in names if n not in ("defined", "sizeof") and not n.endswith("_t")})
+
+
+@pytest.mark.parametrize("header", ["lsb200.h", "lattisense_gpu_runner.h"])
+def test_library_exports_every_declared_symbol(header):
+    lib = C.CDLL(os.path.join(GE.LIB_DIR, "libgpu_mega_ag_runner.so"))
+    names = _declared(header)
+    assert len(names) >= 9
+    for n in names:
+        assert hasattr(lib, n), "missing export " + n
+    if header == "lattisense_gpu_runner.h":
+        for n in ("create_fhe_gpu_task", "release_fhe_gpu_task", "bind_gpu_task_abi_bridge_executors",
+                  "bind_gpu_task_custom_executors", "run_fhe_gpu_task"):
+            assert n in names
+
+
+def _describe(case):
+    h = GE.harness()
+    t = h.th_open(os.path.join(GE.GRAPHS, case).encode(), 1)
+    assert t, h.th_last_error().decode()
+    out = (C.c_longlong * 8)()
+    assert GE.runner_lib().lsb_gpu_task_describe(t, out) == 0
+    return h, t, dict(zip(["computes", "data", "host", "load", "store", "gpu", "fused", "components"], list(out)))
+
+
+def test_bridge_nodes_cfg1():
+    # cfg1: 2 compute nodes, inputs x, y, rlk, one output:
+    # + 3 EXPORT + 3 LOAD + 1 STORE + 1 IMPORT = 10 nodes; mult+relin fuse into one GPU unit
+    h, t, d = _describe("cfg1_bfv_mult")
+    try:
+        assert d["computes"] == 10
+        assert (d["host"], d["load"], d["store"], d["gpu"], d["fused"]) == (4, 3, 1, 1, 1)
+        assert d["data"] == 5 + 3 * 2 + 2
+        assert d["components"] == 1
+    finally:
+        h.th_close(t)
+
+
+def test_components_and_sharding_cfg2():
+    h, t, d = _describe("cfg2_ckks_mult_x8")
+    try:
+        # 8 independent mult->relin->rescale chains sharing only the rlk
+        assert d["components"] == 8 and d["gpu"] == 8 and d["fused"] == 16
+        assert d["load"] == 17 and d["store"] == 8
+        slots = (C.c_int * 8)()
+        for n in (1, 2, 4, 8):
+            assert GE.runner_lib().lsb_gpu_task_shard_preview(t, n, slots, 8) == 8
+            counts = [list(slots).count(s) for s in range(n)]
+            assert counts == [8 // n] * n, counts
+    finally:
+        h.th_close(t)
+
+
+def test_custom_node_splits_device_path():
+    h, t, d = _describe("bfv8k_custom_in_middle")
+    try:
+        # x,y,rlk loaded; (mult,relin) fused; result stored + imported for the custom node; custom output exported
+        # + loaded again for the add; final output stored + imported
+        assert d["gpu"] == 2 and d["fused"] == 1
+        assert d["store"] == 2 and d["load"] == 4
+        assert d["host"] == 4 + 1 + 2  # 4 exports, 1 custom, 2 imports
+    finally:
+        h.th_close(t)
+
+
+@pytest.mark.parametrize("case", GE.all_cases())
+def test_every_fixture_graph_loads(case):
+    h, t, d = _describe(case)
+    try:
+        g = json.load(open(os.path.join(GE.GRAPHS, case, "mega_ag.json")))
+        n_in, n_out = len(g["inputs"]), len(g["outputs"])
+        custom = sum(1 for c in g["compute"].values() if c.get("is_custom"))
+        assert d["computes"] >= len(g["compute"]) + 2 * n_in + 2 * n_out
+        assert d["gpu"] + d["fused"] == len(g["compute"]) - custom
+        assert d["store"] >= n_out and d["load"] >= n_in
+    finally:
+        h.th_close(t)
+
+
+def test_missing_task_directory_is_an_error():
+    h = GE.harness()
+    assert not h.th_open(b"/nonexistent/task", 1)
+    assert "Cannot open MegaAG file" in h.th_last_error().decode()
+
+
+def test_run_without_gpu_fails_loudly():
+    """No CPU fallback: on a box without CUDA the run must fail, not compute on the host."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("CUDA device present")
+    case = GE.GraphCase(os.path.join(GE.GRAPHS, "ckks8k_cac"))
+    with pytest.raises(RuntimeError, match="no CUDA device|CUDA|cuda"):
+        case.run()

@@ -12,9 +12,9 @@
  * abi/c_types.h:26-60.  The `void*` executor parameters are pointers to C++ `ExecutorFunc`
  * objects (see lattisense_mega_ag.hpp) which are copied during the call, exactly as in the reference.
  *
- * Errors: like the reference (gpu_abi_bridge_executors.h:51-55, gpu_wrapper.cu:468) failures inside
- * create/bind/run surface as C++ exceptions (std::runtime_error); run_fhe_gpu_task additionally
- * returns non-zero when a node failed (the SDK turns that into a throw, cxx_fhe_task_gpu.cpp:106-108).
+ * Errors: create/bind throw std::runtime_error like the reference (mega_ag.cpp:136-138); run_fhe_gpu_task
+ * never throws: it returns non-zero when any node failed (the SDK turns that into a throw,
+ * cxx_fhe_task_gpu.cpp:106-108) and lsb_gpu_task_last_error() holds the message.
  * There is no CPU fallback: without a CUDA device run_fhe_gpu_task fails.
  */
 #ifndef LATTISENSE_GPU_RUNNER_H
@@ -125,6 +125,8 @@ int run_fhe_gpu_task(fhe_task_handle handle, CArgument* input_args, uint64_t n_i
 /* Devices used by the NEXT run of this task: independent components of the DAG are sharded over
  * devices[0..n).  Default: the single `gpu_device` passed to run_fhe_gpu_task. */
 void lsb_gpu_task_set_devices(fhe_task_handle handle, const int* devices, int n_devices);
+/* Message of the last failed run_fhe_gpu_task on the calling thread ("" if none). */
+const char* lsb_gpu_task_last_error(void);
 /* Statistics of the last run: kernel launches, batched launch groups, nodes fused away. */
 void lsb_gpu_task_last_stats(fhe_task_handle handle, long long* kernel_launches, long long* batched_groups,
                              long long* fused_nodes);

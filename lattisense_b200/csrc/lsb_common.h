@@ -9,6 +9,7 @@
 #include <memory>
 #include <cuda_runtime.h>
 #include "lsb_math.h"
+#include "lsb_ntt_arith.h"
 
 namespace lsb {
 
@@ -63,6 +64,10 @@ struct ModConst {
     BarrettQ bq;
     Tw ninv;    // N^-1
     Tw w_ninv;  // psi^-1_br[1] * N^-1
+    // FP64 butterfly policy (lsb_ntt_arith.h); f64_ok == 0 for primes that are too wide
+    int f64_ok, f64_recentre;
+    double qd, qinvd;
+    TwD ninv_d, w_ninv_d;
 };
 
 }  // namespace lsb

@@ -60,9 +60,11 @@ Context::Context(int device_, int scheme_, int logN_, const u64* q, int nq_, con
     const int nmod = (int)moduli.size();
     LSB_CHECK(nmod <= 250, "lsb: too many moduli");
     std::vector<Tw> fwd((size_t)nmod * N), inv((size_t)nmod * N);
+    std::vector<TwD> fwd_d((size_t)nmod * N), inv_d((size_t)nmod * N);
     std::vector<ModConst> mc(nmod);
     for (int m = 0; m < nmod; m++) {
-        build_ntt_tables(moduli[m], logN, &fwd[(size_t)m * N], &inv[(size_t)m * N], &mc[m]);
+        build_ntt_tables(moduli[m], logN, &fwd[(size_t)m * N], &inv[(size_t)m * N], &mc[m], &fwd_d[(size_t)m * N],
+                         &inv_d[(size_t)m * N]);
     }
     dt.device = device;
     dt.prof = &prof;
@@ -74,6 +76,10 @@ Context::Context(int device_, int scheme_, int logN_, const u64* q, int nq_, con
     dt.nmod = nmod;
     dt.tw_fwd = (const Tw*)to_device(fwd.data(), fwd.size() * sizeof(Tw));
     dt.tw_inv = (const Tw*)to_device(inv.data(), inv.size() * sizeof(Tw));
+    dt.f64_ok.resize(nmod);
+    for (int m = 0; m < nmod; m++) dt.f64_ok[m] = (uint8_t)mc[m].f64_ok;
+    dt.tw_fwd_d = (const TwD*)to_device(fwd_d.data(), fwd_d.size() * sizeof(TwD));
+    dt.tw_inv_d = (const TwD*)to_device(inv_d.data(), inv_d.size() * sizeof(TwD));
     dt.mods = (const ModConst*)to_device(mc.data(), mc.size() * sizeof(ModConst));
     ws0_.reset(new Workspace(device));
 }

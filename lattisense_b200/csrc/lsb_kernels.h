@@ -13,13 +13,20 @@ struct DeviceTables {
     int nmod = 0;
     const Tw* tw_fwd = nullptr;  // [nmod][N]  psi^bitrev(i) with Shoup companion
     const Tw* tw_inv = nullptr;  // [nmod][N]  psi^-bitrev(i)
+    const TwD* tw_fwd_d = nullptr;  // FP64 policy: (w, w/q) pairs, zero for ineligible primes
+    const TwD* tw_inv_d = nullptr;
     const ModConst* mods = nullptr;
     Profiler* prof = nullptr;
+    std::vector<uint8_t> f64_ok;  // host copy: modulus qualifies for the FP64 butterfly policy
 };
 
 // ---- NTT ----
 void launch_ntt(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap& map, int batch, bool inverse,
                 cudaStream_t s);
+
+// cluster kernel (lsb_ntt_cluster.cu); launch_ntt dispatches to it unless LSB_NTT_IMPL=single
+void launch_ntt_cluster(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap& map, int batch, bool inverse,
+                        const std::vector<uint8_t>& f64_ok, bool allow_f64, cudaStream_t s);
 
 // ---- basis extension (ModUp / ModDown / BFV scaling), Lattigo-style with float64 overflow count ----
 constexpr int kBexMaxSrc = 16;

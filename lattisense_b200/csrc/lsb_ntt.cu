@@ -246,6 +246,18 @@ static void launch_two_pass(NttArgs a, int sms, cudaStream_t s) {
 void launch_ntt(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap& map, int batch, bool inverse,
                 cudaStream_t s) {
     if (batch <= 0 || map.n <= 0) return;
+    static const int impl = [] {  // 0: cluster kernel (default), 1: single-CTA / two-pass kernels
+        const char* e = getenv("LSB_NTT_IMPL");
+        return (e && std::string(e) == "single") ? 1 : 0;
+    }();
+    static const bool allow_f64 = [] {
+        const char* e = getenv("LSB_NTT_F64");
+        return !(e && atoi(e) == 0);
+    }();
+    if (impl == 0) {
+        launch_ntt_cluster(dt, in, out, map, batch, inverse, dt.f64_ok, allow_f64, s);
+        return;
+    }
     NttArgs a;
     a.in = in;
     a.out = out;

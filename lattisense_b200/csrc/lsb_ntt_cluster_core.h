@@ -1,0 +1,47 @@
+// Shared-memory round of the cluster NTT (LSB_HD so that tests/emul can run it on the CPU).
+#pragma once
+#include "lsb_ntt_arith.h"
+#include "lsb_ntt_core.h"
+
+namespace lsb {
+
+// one local round on sub-tile `smt` (BS words, swizzled): LR stages starting at local stage v
+template <class P, int LR, bool INV, bool RAW_SRC, bool CANON>
+LSB_HD void local_round(u64* smt, const typename P::TW* __restrict__ tw, int g, int logGC, int v,
+                                            u32 twbase, const ModCtx& m) {
+    constexpr int R = 1 << LR;
+    const int hi = g >> logGC;
+    const int u0 = (hi << (LR + logGC)) + (g & ((1 << logGC) - 1));
+    typename P::V x[R];
+    if (logGC == 0) {
+#pragma unroll
+        for (int k = 0; k < R; k += 2) {
+            const W2 pr = *reinterpret_cast<const W2*>(&smt[swz(u0 + k)]);
+            x[k] = RAW_SRC ? P::from_raw(pr.a) : P::from_bits(pr.a);
+            x[k + 1] = RAW_SRC ? P::from_raw(pr.b) : P::from_bits(pr.b);
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < R; k++) {
+            const u64 b = smt[swz(u0 + (k << logGC))];
+            x[k] = RAW_SRC ? P::from_raw(b) : P::from_bits(b);
+        }
+    }
+    const u32 tbase = (twbase << v) + (u32)hi;
+    if (!INV) fwd_stages<P, LR>(x, tw, tbase, m);
+    else inv_stages<P, LR, false>(x, tw, tbase, m, typename P::TW{}, typename P::TW{});
+    if (logGC == 0) {
+#pragma unroll
+        for (int k = 0; k < R; k += 2) {
+            W2 pr;
+            pr.a = CANON ? P::fwd_canonical(x[k], m) : P::to_bits(x[k]);
+            pr.b = CANON ? P::fwd_canonical(x[k + 1], m) : P::to_bits(x[k + 1]);
+            *reinterpret_cast<W2*>(&smt[swz(u0 + k)]) = pr;
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < R; k++) smt[swz(u0 + (k << logGC))] = CANON ? P::fwd_canonical(x[k], m) : P::to_bits(x[k]);
+    }
+}
+
+}  // namespace lsb

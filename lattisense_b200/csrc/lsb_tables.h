@@ -9,7 +9,9 @@ namespace lsb {
 
 // fwd/inv: N entries each.  psi = g^((q-1)/2N), g the smallest generator of Z_q^* (Lattigo ring.NTT
 // parameters); tables hold psi^bitrev(j) / psi^-bitrev(j) with Shoup companions.
-inline void build_ntt_tables(u64 qq, int logN, Tw* f, Tw* iv, ModConst* mc) {
+inline TwD make_twd(u64 w, u64 q) { return TwD{(double)w, (double)w / (double)q}; }
+
+inline void build_ntt_tables(u64 qq, int logN, Tw* f, Tw* iv, ModConst* mc, TwD* fd = nullptr, TwD* ivd = nullptr) {
     using namespace host;
     const u64 N = 1ull << logN;
     LSB_CHECK(qq < (1ull << 62), "lsb: modulus must be below 2^62");
@@ -31,6 +33,17 @@ inline void build_ntt_tables(u64 qq, int logN, Tw* f, Tw* iv, ModConst* mc) {
     mc->bq = make_barrett(qq);
     mc->ninv = make_tw(ninv, qq);
     mc->w_ninv = make_tw(mulmod(iv[1].w, ninv, qq), qq);
+    mc->f64_ok = f64_eligible(qq, logN) ? 1 : 0;
+    mc->f64_recentre = f64_needs_recentre(qq, logN) ? 1 : 0;
+    mc->qd = (double)qq;
+    mc->qinvd = 1.0 / (double)qq;
+    mc->ninv_d = make_twd(mc->ninv.w, qq);
+    mc->w_ninv_d = make_twd(mc->w_ninv.w, qq);
+    if (fd && ivd)
+        for (u64 j = 0; j < N; j++) {
+            fd[j] = mc->f64_ok ? make_twd(f[j].w, qq) : TwD{0.0, 0.0};
+            ivd[j] = mc->f64_ok ? make_twd(iv[j].w, qq) : TwD{0.0, 0.0};
+        }
 }
 
 // CRT tables for extending residues from the moduli `src` to each modulus of `dst` (indices into `moduli`).

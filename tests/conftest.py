@@ -29,6 +29,7 @@ def emul():
     u64p = C.POINTER(C.c_uint64)
     i32p = C.POINTER(C.c_int)
     lib.emul_ntt.argtypes = [C.c_int, C.c_uint64, u64p, C.c_int, C.c_int]
+    lib.emul_ntt_cluster.argtypes = [C.c_int, C.c_uint64, u64p, C.c_int, C.c_int]
     lib.emul_basis_extend.argtypes = [C.c_int, u64p, C.c_int, i32p, C.c_int, i32p, C.c_int, C.c_int, u64p, u64p]
     for n in ("emul_mulmod", "emul_barrett64", "emul_mul_shoup"):
         getattr(lib, n).restype = C.c_uint64

@@ -6,6 +6,7 @@
 #include "../../lattisense_b200/csrc/lsb_ntt_core.h"
 #include "../../lattisense_b200/csrc/lsb_tables.h"
 #include "../../lattisense_b200/csrc/lsb_elem_core.h"
+#include "../../lattisense_b200/csrc/lsb_ntt_cluster_core.h"
 
 using namespace lsb;
 
@@ -114,7 +115,86 @@ static void rows_pass(int logN, const Tw* tw, const ModConst& mc, u64* data, boo
     }
 }
 
+// mirrors k_ntt_cluster (lsb_ntt_cluster.cu): cross radix-16 round + local rounds per 1/16 block; the CTA
+// split is irrelevant on the CPU (blocks are independent), the index / twiddle / arithmetic code is the same
+template <class P, int LR, bool INV, bool RAW, bool CANON>
+static void local_all(int logN, int i_round, const Plan& PL, u64* sm, const typename P::TW* tw, const ModCtx& m) {
+    const int BS = (1 << logN) / 16, GPB = BS >> LR, loggc = plan_loggc(PL, i_round);
+    for (int blk = 0; blk < 16; blk++)
+        for (int g = 0; g < GPB; g++)
+            local_round<P, LR, INV, RAW, CANON>(sm + blk * BS, tw, g, loggc, PL.rounds[i_round].v, 16u + (u32)blk, m);
+}
+template <class P, bool INV>
+static void local_dyn(int logN, int i, const Plan& PL, u64* sm, const typename P::TW* tw, const ModCtx& m, bool raw, bool canon) {
+    const int lr = PL.rounds[i].lr;
+#define LCASE(LR, RAW, CANON) \
+    if (lr == LR && raw == RAW && canon == CANON) return local_all<P, LR, INV, RAW, CANON>(logN, i, PL, sm, tw, m);
+    LCASE(3, false, false) LCASE(3, true, false) LCASE(3, false, true) LCASE(4, false, false) LCASE(4, true, false) LCASE(4, false, true)
+    throw std::runtime_error("emul: unhandled cluster round");
+}
+template <class P>
+static void cluster_ntt(int logN, const typename P::TW* tw, const ModConst& mc, typename P::TW ninv, typename P::TW w_ninv, u64* data,
+                        bool inverse) {
+    const int N = 1 << logN, BS = N / 16;
+    const Plan PL = make_plan(logN - 4, 0);
+    ModCtx m;
+    m.q = mc.q;
+    m.q2 = mc.q << 1;
+    m.qinv64 = mc.qinv64;
+    m.qd = mc.qd;
+    m.qinvd = mc.qinvd;
+    m.lazy = mc.q < kLazyLimit;
+    m.recentre = mc.f64_recentre != 0;
+    std::vector<u64> sm(N);
+    if (!inverse) {
+        for (int g = 0; g < BS; g++) {
+            typename P::V x[16];
+            for (int k = 0; k < 16; k++) x[k] = P::from_raw(data[g + k * BS]);
+            fwd_stages<P, 4>(x, tw, 1u, m);
+            for (int k = 0; k < 16; k++) sm[k * BS + swz(g)] = P::to_bits(x[k]);
+        }
+        for (int i = 0; i < PL.nrounds; i++) local_dyn<P, false>(logN, i, PL, sm.data(), tw, m, false, i == PL.nrounds - 1);
+        for (int c = 0; c < N / 2; c++) {
+            data[2 * c] = sm[swz(2 * c)];
+            data[2 * c + 1] = sm[swz(2 * c) + 1];
+        }
+    } else {
+        for (int c = 0; c < N / 2; c++) {
+            sm[swz(2 * c)] = data[2 * c];
+            sm[swz(2 * c) + 1] = data[2 * c + 1];
+        }
+        for (int i = PL.nrounds - 1; i >= 0; i--) local_dyn<P, true>(logN, i, PL, sm.data(), tw, m, i == PL.nrounds - 1, false);
+        for (int g = 0; g < BS; g++) {
+            typename P::V x[16];
+            for (int k = 0; k < 16; k++) x[k] = P::from_bits(sm[k * BS + swz(g)]);
+            inv_stages<P, 4, true>(x, tw, 1u, m, ninv, w_ninv);
+            for (int k = 0; k < 16; k++) data[g + k * BS] = P::inv_canonical(x[k], m);
+        }
+    }
+}
+
 extern "C" {
+
+// f64: 1 = FP64 butterfly policy (returns 2 if the prime does not qualify), 0 = 64-bit Shoup/Harvey policy
+int emul_ntt_cluster(int logN, u64 q, u64* data, int inverse, int f64) {
+    try {
+        const int N = 1 << logN;
+        std::vector<Tw> f(N), iv(N);
+        std::vector<TwD> fd(N), ivd(N);
+        ModConst mc;
+        build_ntt_tables(q, logN, f.data(), iv.data(), &mc, fd.data(), ivd.data());
+        if (f64) {
+            if (!mc.f64_ok) return 2;
+            cluster_ntt<ArithF64>(logN, inverse ? ivd.data() : fd.data(), mc, mc.ninv_d, mc.w_ninv_d, data, inverse != 0);
+        } else {
+            cluster_ntt<ArithU64>(logN, inverse ? iv.data() : f.data(), mc, mc.ninv, mc.w_ninv, data, inverse != 0);
+        }
+        return 0;
+    } catch (const std::exception& e) {
+        fprintf(stderr, "emul_ntt_cluster: %s\n", e.what());
+        return 1;
+    }
+}
 
 int emul_ntt(int logN, u64 q, u64* data, int inverse, int nthreads) {
     try {

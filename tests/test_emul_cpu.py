@@ -99,3 +99,35 @@ def test_barrett_and_shoup(emul):
             assert emul.emul_mul_shoup(x, b, q) == x * b % q
         for a, b in [(0, 0), (q - 1, q - 1), (1, q - 1), (q - 1, 1)]:
             assert emul.emul_mulmod(a, b, q) == a * b % q
+
+
+@pytest.mark.parametrize("params", [R.CKKS_N12, R.CKKS_N13, R.CKKS_N14, R.BFV_N13, R.CKKS_BTP_N15, R.CKKS_BTP_N16],
+                         ids=lambda p: p.name)
+def test_cluster_ntt_both_policies_match_oracle(emul, params):
+    """k_ntt_cluster's round code on the CPU: the FP64 policy (eligible primes) and the 64-bit policy give the
+    oracle's limbs bit for bit, forward and inverse, including extreme residues."""
+    o = R.Oracle(params)
+    rng = np.random.default_rng(5)
+    n_f64 = 0
+    mids = range(o.nmods) if params.logN <= 14 else [0, 1, 9, 12, 24, 25, 29]
+    for mid in mids:
+        q = o.moduli[mid]
+        a = rng.integers(0, q, size=params.N, dtype=np.uint64)
+        a[:4] = [0, 1, q - 1, q // 2]
+        worst = np.full(params.N, q - 1, dtype=np.uint64)
+        for f64 in (0, 1):
+            for vec in (a, worst):
+                fwd = vec.copy()
+                rc = emul.emul_ntt_cluster(params.logN, q, R.P(fwd), 0, f64)
+                if rc == 2:
+                    assert f64 == 1 and q * (params.logN + 1) >= 2 ** 51
+                    break
+                assert rc == 0
+                assert np.array_equal(fwd, o.ntt(mid, vec))
+                inv = vec.copy()
+                assert emul.emul_ntt_cluster(params.logN, q, R.P(inv), 1, f64) == 0
+                assert np.array_equal(inv, o.ntt(mid, vec, inverse=True))
+            else:
+                n_f64 += f64
+    if params.scheme == R.SCHEME_CKKS and params.logN <= 14:
+        assert n_f64 == o.nmods  # every default CKKS prime takes the FP64 path

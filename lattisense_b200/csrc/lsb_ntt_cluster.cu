@@ -19,6 +19,12 @@
 #include "lsb_ntt_core.h"
 #include "lsb_ntt_cluster_core.h"
 
+#ifndef LSB_CL_MINB
+#define LSB_CL_MINB 4
+#endif
+#ifndef LSB_CL_NT
+#define LSB_CL_NT 256
+#endif
 namespace cg = cooperative_groups;
 
 namespace lsb {
@@ -31,7 +37,7 @@ struct ClusterCfg {
     static constexpr int LS = LOGN - 4;
     static constexpr int NB = 16 / CL;      // blocks per CTA
     static constexpr int TILE = N / CL;     // words of shared memory per CTA
-    static constexpr int NT = 256;
+    static constexpr int NT = LSB_CL_NT;
     static constexpr int G0 = BS / CL;      // cross-round groups per CTA
 };
 
@@ -59,7 +65,7 @@ __device__ __forceinline__ const typename P::TW* tw_of(const NttClArgs& a, int m
 }
 
 template <int LOGN, bool INV, class P>
-__global__ void __launch_bounds__(ClusterCfg<LOGN>::NT, 3) k_ntt_cluster(const __grid_constant__ NttClArgs a) {
+__global__ void __launch_bounds__(ClusterCfg<LOGN>::NT, LSB_CL_MINB) k_ntt_cluster(const __grid_constant__ NttClArgs a) {
     typedef ClusterCfg<LOGN> C;
     extern __shared__ __align__(1024) u64 sm[];
     constexpr int N = C::N, CL = C::CL, BS = C::BS, NB = C::NB, TILE = C::TILE, NT = C::NT;
@@ -108,16 +114,14 @@ __global__ void __launch_bounds__(ClusterCfg<LOGN>::NT, 3) k_ntt_cluster(const _
             constexpr int GPB = BS >> lr;  // groups per block
             for (int gg = tid; gg < NB * GPB; gg += NT) {
                 const int st = gg / GPB, g = gg - st * GPB;
-                local_round<P, lr, false, false, last>(sm + st * BS, tw, g, loggc, PL.rounds[i].v, 16u + (u32)(rank * NB + st), m);
+                local_round<P, lr, false, false, last>(sm + st * BS, tw, g, loggc, PL.rounds[i].v, 16u + (u32)(rank * NB + st), m,
+                                                       nullptr, nullptr);
             }
             __syncthreads();
         });
         u64* out = dst + (size_t)rank * TILE;
         for (int c = tid; c < TILE / 2; c += NT) reinterpret_cast<W2*>(out)[c] = *reinterpret_cast<const W2*>(&sm[swz(2 * c)]);
     } else {
-        const u64* inp = src + (size_t)rank * TILE;
-        for (int c = tid; c < TILE / 2; c += NT) *reinterpret_cast<W2*>(&sm[swz(2 * c)]) = reinterpret_cast<const W2*>(inp)[c];
-        __syncthreads();
         static_for_cl<0, PL.nrounds>([&](auto ic) {
             constexpr int i = PL.nrounds - 1 - decltype(ic)::value;
             constexpr int lr = PL.rounds[i].lr;
@@ -126,7 +130,8 @@ __global__ void __launch_bounds__(ClusterCfg<LOGN>::NT, 3) k_ntt_cluster(const _
             constexpr int GPB = BS >> lr;
             for (int gg = tid; gg < NB * GPB; gg += NT) {
                 const int st = gg / GPB, g = gg - st * GPB;
-                local_round<P, lr, true, first, false>(sm + st * BS, tw, g, loggc, PL.rounds[i].v, 16u + (u32)(rank * NB + st), m);
+                local_round<P, lr, true, first, false>(sm + st * BS, tw, g, loggc, PL.rounds[i].v, 16u + (u32)(rank * NB + st), m,
+                                                       src + (size_t)rank * TILE + st * BS);
             }
             __syncthreads();
         });

@@ -5,10 +5,14 @@
 
 namespace lsb {
 
-// one local round on sub-tile `smt` (BS words, swizzled): LR stages starting at local stage v
+// one local round on sub-tile `smt` (BS words, swizzled): LR stages starting at local stage v.
+// RAW_SRC (first inverse round): canonical residues are read straight from global memory `gsrc` (block base);
+// CANON (last forward round): canonical residues are written to global memory `gdst` if given (measured
+// slower than staging through shared memory on B200: half-sector stores), else to shared memory.  Both only
+// occur in the contiguous round (logGC == 0), where a thread owns 2^LR consecutive words.
 template <class P, int LR, bool INV, bool RAW_SRC, bool CANON>
-LSB_HD void local_round(u64* smt, const typename P::TW* __restrict__ tw, int g, int logGC, int v,
-                                            u32 twbase, const ModCtx& m) {
+LSB_HD void local_round(u64* smt, const typename P::TW* __restrict__ tw, int g, int logGC, int v, u32 twbase,
+                        const ModCtx& m, const u64* __restrict__ gsrc = nullptr, u64* __restrict__ gdst = nullptr) {
     constexpr int R = 1 << LR;
     const int hi = g >> logGC;
     const int u0 = (hi << (LR + logGC)) + (g & ((1 << logGC) - 1));
@@ -16,7 +20,7 @@ LSB_HD void local_round(u64* smt, const typename P::TW* __restrict__ tw, int g, 
     if (logGC == 0) {
 #pragma unroll
         for (int k = 0; k < R; k += 2) {
-            const W2 pr = *reinterpret_cast<const W2*>(&smt[swz(u0 + k)]);
+            const W2 pr = RAW_SRC ? *reinterpret_cast<const W2*>(&gsrc[u0 + k]) : *reinterpret_cast<const W2*>(&smt[swz(u0 + k)]);
             x[k] = RAW_SRC ? P::from_raw(pr.a) : P::from_bits(pr.a);
             x[k + 1] = RAW_SRC ? P::from_raw(pr.b) : P::from_bits(pr.b);
         }
@@ -36,7 +40,8 @@ LSB_HD void local_round(u64* smt, const typename P::TW* __restrict__ tw, int g, 
             W2 pr;
             pr.a = CANON ? P::fwd_canonical(x[k], m) : P::to_bits(x[k]);
             pr.b = CANON ? P::fwd_canonical(x[k + 1], m) : P::to_bits(x[k + 1]);
-            *reinterpret_cast<W2*>(&smt[swz(u0 + k)]) = pr;
+            if (CANON && gdst) *reinterpret_cast<W2*>(&gdst[u0 + k]) = pr;
+            else *reinterpret_cast<W2*>(&smt[swz(u0 + k)]) = pr;
         }
     } else {
 #pragma unroll

@@ -118,17 +118,19 @@ static void rows_pass(int logN, const Tw* tw, const ModConst& mc, u64* data, boo
 // mirrors k_ntt_cluster (lsb_ntt_cluster.cu): cross radix-16 round + local rounds per 1/16 block; the CTA
 // split is irrelevant on the CPU (blocks are independent), the index / twiddle / arithmetic code is the same
 template <class P, int LR, bool INV, bool RAW, bool CANON>
-static void local_all(int logN, int i_round, const Plan& PL, u64* sm, const typename P::TW* tw, const ModCtx& m) {
+static void local_all(int logN, int i_round, const Plan& PL, u64* sm, const typename P::TW* tw, const ModCtx& m, u64* gio) {
     const int BS = (1 << logN) / 16, GPB = BS >> LR, loggc = plan_loggc(PL, i_round);
     for (int blk = 0; blk < 16; blk++)
         for (int g = 0; g < GPB; g++)
-            local_round<P, LR, INV, RAW, CANON>(sm + blk * BS, tw, g, loggc, PL.rounds[i_round].v, 16u + (u32)blk, m);
+            local_round<P, LR, INV, RAW, CANON>(sm + blk * BS, tw, g, loggc, PL.rounds[i_round].v, 16u + (u32)blk, m, gio + blk * BS,
+                                                gio + blk * BS);
 }
 template <class P, bool INV>
-static void local_dyn(int logN, int i, const Plan& PL, u64* sm, const typename P::TW* tw, const ModCtx& m, bool raw, bool canon) {
+static void local_dyn(int logN, int i, const Plan& PL, u64* sm, const typename P::TW* tw, const ModCtx& m, bool raw, bool canon,
+                      u64* gio) {
     const int lr = PL.rounds[i].lr;
 #define LCASE(LR, RAW, CANON) \
-    if (lr == LR && raw == RAW && canon == CANON) return local_all<P, LR, INV, RAW, CANON>(logN, i, PL, sm, tw, m);
+    if (lr == LR && raw == RAW && canon == CANON) return local_all<P, LR, INV, RAW, CANON>(logN, i, PL, sm, tw, m, gio);
     LCASE(3, false, false) LCASE(3, true, false) LCASE(3, false, true) LCASE(4, false, false) LCASE(4, true, false) LCASE(4, false, true)
     throw std::runtime_error("emul: unhandled cluster round");
 }
@@ -153,17 +155,10 @@ static void cluster_ntt(int logN, const typename P::TW* tw, const ModConst& mc, 
             fwd_stages<P, 4>(x, tw, 1u, m);
             for (int k = 0; k < 16; k++) sm[k * BS + swz(g)] = P::to_bits(x[k]);
         }
-        for (int i = 0; i < PL.nrounds; i++) local_dyn<P, false>(logN, i, PL, sm.data(), tw, m, false, i == PL.nrounds - 1);
-        for (int c = 0; c < N / 2; c++) {
-            data[2 * c] = sm[swz(2 * c)];
-            data[2 * c + 1] = sm[swz(2 * c) + 1];
-        }
+        for (int i = 0; i < PL.nrounds; i++) local_dyn<P, false>(logN, i, PL, sm.data(), tw, m, false, i == PL.nrounds - 1, data);
+        (void)sm;
     } else {
-        for (int c = 0; c < N / 2; c++) {
-            sm[swz(2 * c)] = data[2 * c];
-            sm[swz(2 * c) + 1] = data[2 * c + 1];
-        }
-        for (int i = PL.nrounds - 1; i >= 0; i--) local_dyn<P, true>(logN, i, PL, sm.data(), tw, m, i == PL.nrounds - 1, false);
+        for (int i = PL.nrounds - 1; i >= 0; i--) local_dyn<P, true>(logN, i, PL, sm.data(), tw, m, i == PL.nrounds - 1, false, data);
         for (int g = 0; g < BS; g++) {
             typename P::V x[16];
             for (int k = 0; k < 16; k++) x[k] = P::from_bits(sm[k * BS + swz(g)]);

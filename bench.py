@@ -145,6 +145,106 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+# ---------------------------------------------------------------------------------------------
+# API-level arm: the same workload through the reference-facing boundary (run_fhe_gpu_task)
+# ---------------------------------------------------------------------------------------------
+def write_cfg2_task(path, B, P):
+    """mega_ag.json / task_signature.json of B independent z_i = rescale(mult_relin(x_i, y_i)) at level 3 in the
+    format frontend/custom_task.py emits (field for field the committed fixture tests/golden/graphs/cfg2_ckks_mult_x8,
+    which the reference frontend generated; here only the copy count differs)."""
+    os.makedirs(path, exist_ok=True)
+    ct = lambda i, lv, deg=1, t="ct": {"id": i, "type": t, "level": lv, "degree": deg, "is_ntt": True, "is_mform": False,
+                                       "poly1_rns_sp_decomped": False}
+    data, comp = {}, {}
+    nd = 0
+    xs, ys, zs = [], [], []
+    for i in range(B):
+        data[str(nd)] = ct("x_%d" % i, LEVEL); xs.append(nd); nd += 1
+    for i in range(B):
+        data[str(nd)] = ct("y_%d" % i, LEVEL); ys.append(nd); nd += 1
+    rlk = nd
+    data[str(nd)] = {"id": "rlk_ntt", "type": "rlk", "level": LEVEL, "degree": 1, "is_ntt": True, "is_mform": True, "sp_level": len(P.p) - 1}
+    nd += 1
+    nc = 0
+    for i in range(B):
+        c3, r = nd, nd + 1
+        z = nd + 2
+        nd += 3
+        data[str(c3)] = ct("t3_%d" % i, LEVEL, 2, "ct3")
+        data[str(r)] = ct("t2_%d" % i, LEVEL)
+        data[str(z)] = ct("z_%d" % i, LEVEL - 1)
+        comp[str(nc)] = {"id": "m%d" % i, "type": "mult", "inputs": [xs[i], ys[i]], "outputs": [c3]}
+        comp[str(nc + 1)] = {"id": "r%d" % i, "type": "relin", "inputs": [c3, rlk], "outputs": [r]}
+        comp[str(nc + 2)] = {"id": "s%d" % i, "type": "rescale", "inputs": [r], "outputs": [z]}
+        nc += 3
+        zs.append(z)
+    g = {"name": "Acc task", "algorithm": "CKKS", "data": data, "compute": comp, "inputs": xs + ys + [rlk], "outputs": zs,
+         "offline_inputs": [], "parameter": {"n": P.N, "max_level": len(P.q) - 1, "q": P.q, "p": P.p, "slots": P.N // 2, "scale": P.scale}}
+    sig = {"algorithm": "CKKS", "key": {"rlk": LEVEL, "glk": {}},
+           "online": [{"id": "in_x_list", "type": "ct", "size": [B], "level": LEVEL, "phase": "in"},
+                      {"id": "in_y_list", "type": "ct", "size": [B], "level": LEVEL, "phase": "in"},
+                      {"id": "out_z_list", "type": "ct", "size": [B], "level": LEVEL - 1, "phase": "out"}], "offline": []}
+    with open(os.path.join(path, "mega_ag.json"), "w") as f:
+        json.dump(g, f)
+    with open(os.path.join(path, "task_signature.json"), "w") as f:
+        json.dump(sig, f)
+
+
+class RunnerArm:
+    """Drives create_/bind_/run_/release_fhe_gpu_task the way FheTaskGpu does (cxx_sdk_v2/cxx_fhe_task_gpu.cpp:69-117),
+    with the test plug-in's EXPORT/IMPORT executors over host limb buffers (tests/harness/harness.cpp)."""
+
+    def __init__(self, P, B, a_host, b_host, rlk_host, out_host, device, tag):
+        import ctypes as C
+        import tempfile
+        import graph_eval as GE
+        self.C, self.GE, self.B, self.device = C, GE, B, device
+        self.dir = tempfile.mkdtemp(prefix="lsb_cfg2_%s_" % tag)
+        write_cfg2_task(self.dir, B, P)
+        self.h = GE.harness()
+        self.task = self.h.th_open(self.dir.encode(), 1)
+        if not self.task:
+            raise RuntimeError("th_open: " + self.h.th_last_error().decode())
+        u64p = C.POINTER(C.c_uint64)
+
+        def handle(ptr, kind, level, degree):
+            t = GE.THandle()
+            t.kind, t.level, t.degree, t.n, t.k = kind, level, degree, P.N, len(P.p)
+            t.data = C.cast(ptr, u64p)
+            return t
+
+        l = LEVEL + 1
+        ct_bytes = 2 * l * P.N * 8
+        self.h_in = [handle(a_host.data_ptr() + i * ct_bytes, 0, LEVEL, 1) for i in range(B)]
+        self.h_in += [handle(b_host.data_ptr() + i * ct_bytes, 0, LEVEL, 1) for i in range(B)]
+        self.h_in.append(handle(rlk_host.data_ptr(), 3, LEVEL, 1))
+        out_bytes = 2 * (l - 1) * P.N * 8
+        self.h_out = [handle(out_host.data_ptr() + i * out_bytes, 0, LEVEL - 1, 1) for i in range(B)]
+        ia = lambda v: (C.c_int * len(v))(*v)
+        self.in_meta = (ia([GE.TYPE_CIPHERTEXT, GE.TYPE_CIPHERTEXT, GE.TYPE_RELIN_KEY]), ia([LEVEL, LEVEL, LEVEL]), ia([B, B, 1]))
+        self.out_meta = (ia([GE.TYPE_CIPHERTEXT]), ia([LEVEL - 1]), ia([B]))
+        self.in_ptrs = (C.POINTER(GE.THandle) * len(self.h_in))(*[C.pointer(x) for x in self.h_in])
+        self.out_ptrs = (C.POINTER(GE.THandle) * len(self.h_out))(*[C.pointer(x) for x in self.h_out])
+        self.prog = (C.c_int * 3)()
+
+    def step(self):
+        rc = self.h.th_run(self.task, 3, self.in_meta[0], self.in_meta[1], self.in_meta[2], self.in_ptrs, 1, self.out_meta[0],
+                           self.out_meta[1], self.out_meta[2], self.out_ptrs, self.device, self.prog)
+        if rc != 0:
+            raise RuntimeError("run_fhe_gpu_task failed: " + self.h.th_last_error().decode())
+
+    def stats(self):
+        C = self.C
+        st = [C.c_longlong() for _ in range(3)]
+        self.GE.runner_lib().lsb_gpu_task_last_stats(self.task, *[C.byref(x) for x in st])
+        return tuple(x.value for x in st)
+
+    def close(self):
+        import shutil
+        self.h.th_close(self.task)
+        shutil.rmtree(self.dir, ignore_errors=True)
+
+
 def run_ours(args):
     import ctypes as C
     import torch
@@ -225,11 +325,41 @@ def run_ours(args):
     clocks = sampler.summary()
     value = world * B * args.steps / (ms / 1e3)
 
-    # end-to-end through the C ABI with host buffers
+    # end-to-end through the kernel-level C ABI with host buffers
     step_e2e()
     e2e_steps = max(1, min(args.steps, 5))
     ms_e2e = timed(step_e2e, e2e_steps)
     e2e_value = world * B * e2e_steps / (ms_e2e / 1e3)
+
+    # end-to-end through the reference boundary: run_fhe_gpu_task on a 3*B-node mega_ag graph, host limb buffers in,
+    # EXPORT -> pinned staging -> H2D -> batched kernels -> D2H -> IMPORT into host buffers out (wall clock: the call is
+    # synchronous, exactly what FheTaskGpu::run returns, cxx_fhe_task_gpu.cpp:110-116)
+    api = None
+    if not args.no_api:
+        rlk_host = rlk_dev.cpu()
+        arm = RunnerArm(P, B, a_host, b_host, rlk_host, out_host, local, "r%d" % rank)
+        try:
+            arm.step()  # warm-up: context, tables, pools, key upload
+            arm.step()
+            api_steps = max(1, min(args.steps, 5))
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(api_steps):
+                arm.step()
+            torch.cuda.synchronize()
+            dt = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+            if world > 1:
+                dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+            dt = float(dt.item())
+            st = arm.stats()
+            api = {"value": world * B * api_steps / dt, "unit": UNIT, "ms_per_step": 1e3 * dt / api_steps,
+                   "h2d_bytes_per_step": (a_host.numel() + b_host.numel()) * 8, "d2h_bytes_per_step": out_host.numel() * 8,
+                   "path": "create_/bind_/run_fhe_gpu_task (include/lattisense_gpu_runner.h), %d-node mega_ag graph, "
+                           "test plug-in EXPORT/IMPORT over host limb buffers" % (3 * B),
+                   "runner_stats": {"kernel_launches": st[0], "batched_groups": st[1], "fused_nodes": st[2]},
+                   "matches_device_path": bool(torch.equal(out_host, out_dev.cpu()))}
+        finally:
+            arm.close()
 
     # roofline pass: per-kernel-class CUDA events on the launching stream (one extra step, same inputs)
     ctx.profile(True)
@@ -269,9 +399,10 @@ def run_ours(args):
         "config": {"workload": "CKKS mult_relin+rescale n=16384 level 3->2 (BASELINE configs[1])",
                    "batch_per_gpu": B, "l2": "inputs (2 GiB/step) larger than L2, no flush needed",
                    "parallelism": "batch-sharded x%d, no collective" % world},
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": (a_host.numel() + b_host.numel()) * 8,
-                "d2h_bytes_per_step": out_host.numel() * 8, "ms_per_step": ms_e2e / e2e_steps,
-                "path": "C ABI lsb_upload + lsb_mult_relin_rescale + lsb_download, pinned host buffers"},
+        "e2e": api if api is not None else None,
+        "e2e_kernel_abi": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": (a_host.numel() + b_host.numel()) * 8,
+                           "d2h_bytes_per_step": out_host.numel() * 8, "ms_per_step": ms_e2e / e2e_steps,
+                           "path": "C ABI lsb_upload + lsb_mult_relin_rescale + lsb_download (include/lsb200.h), pinned host buffers"},
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": "k_ntt_single<14> (fwd+inv, in-step average)",
@@ -293,6 +424,7 @@ def main():
     ap.add_argument("--batch", type=int, default=1024)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-api", action="store_true", help="skip the run_fhe_gpu_task end-to-end leg")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -33,6 +33,10 @@ void* Context::to_device(const void* host_ptr, size_t bytes) {
     LSB_CUDA(cudaSetDevice(device));
     LSB_CUDA(cudaMalloc(&d, bytes));
     LSB_CUDA(cudaMemcpy(d, host_ptr, bytes, cudaMemcpyHostToDevice));
+    // a pageable H2D cudaMemcpy may return once the data sits in the driver's staging buffer, before the DMA
+    // has landed; the kernels that read these tables run on non-blocking streams, which do not order
+    // against the legacy stream, so wait for the DMA here (tables are built once and cached)
+    LSB_CUDA(cudaStreamSynchronize(cudaStreamLegacy));
     owned_.push_back(d);
     return d;
 }

@@ -1,6 +1,7 @@
 // Context construction and cached table builders (host side).
 #include "lsb_context.h"
 #include "lsb_tables.h"
+#include "lsb_ntt_cluster_core.h"
 #include <cstring>
 
 namespace lsb {
@@ -85,6 +86,19 @@ Context::Context(int device_, int scheme_, int logN_, const u64* q, int nq_, con
     dt.tw_fwd_d = (const TwD*)to_device(fwd_d.data(), fwd_d.size() * sizeof(TwD));
     dt.tw_inv_d = (const TwD*)to_device(inv_d.data(), inv_d.size() * sizeof(TwD));
     dt.mods = (const ModConst*)to_device(mc.data(), mc.size() * sizeof(ModConst));
+    {
+        const int lrl = cluster_last_lr(logN);
+        for (int m = 0; m < nmod; m++) {
+            soa_tail(&fwd[(size_t)m * N], logN, lrl);
+            soa_tail(&inv[(size_t)m * N], logN, lrl);
+            soa_tail(&fwd_d[(size_t)m * N], logN, lrl);
+            soa_tail(&inv_d[(size_t)m * N], logN, lrl);
+        }
+        dt.twc_fwd = (const Tw*)to_device(fwd.data(), fwd.size() * sizeof(Tw));
+        dt.twc_inv = (const Tw*)to_device(inv.data(), inv.size() * sizeof(Tw));
+        dt.twc_fwd_d = (const TwD*)to_device(fwd_d.data(), fwd_d.size() * sizeof(TwD));
+        dt.twc_inv_d = (const TwD*)to_device(inv_d.data(), inv_d.size() * sizeof(TwD));
+    }
     ws0_.reset(new Workspace(device));
 }
 

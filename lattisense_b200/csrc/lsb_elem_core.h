@@ -33,7 +33,7 @@ LSB_HD void bex_coeff(const BexJob& job, const ModConst* mods, const u64* x, Oth
         const ModConst& m = mods[job.dst_mod[t]];
         Acc128 acc{0, 0};
         for (int i = 0; i < job.ns; i++) acc_mad(acc, y[i], job.qhat_mod[t][i]);
-        u64 e = barrett128(acc.lo, acc.hi, m.bq);
+        u64 e = job.wide_ok ? reduce_wide(acc.lo, acc.hi, m.bq) : barrett128(acc.lo, acc.hi, m.bq);
         e = submod(e, job.vS[t][v], m.q);
         if (job.mode == BEX_OTHER_SUB) {
             u64 d = submod(other(t), e, m.q);

@@ -25,7 +25,14 @@ inline u64 shoup(u64 w, u64 q) { return (u64)(((u128)w << 64) / q); }
 inline Tw make_tw(u64 w, u64 q) { return Tw{w, shoup(w, q)}; }
 inline BarrettQ make_barrett(u64 q) {
     u128 r = ~(u128)0 / q;  // floor((2^128-1)/q) == floor(2^128/q) for odd q > 1
-    return BarrettQ{q, (u64)r, (u64)(r >> 64)};
+    u32 sh = 0;
+    while (sh < 63 && (q >> (sh + 1))) sh++;  // bitlen(q) - 1
+    if (sh == 0) sh = 1;                      // q < 2 never occurs; keeps the shifts in range
+    // q == 2^sh (a power-of-two plaintext modulus) would need mu = 2^64: use 2^64 - 1, the estimate is then low by
+    // at most one more unit, still within the two conditional subtractions of reduce_wide
+    const u128 mu_full = ((u128)1 << (sh + 64)) / q;
+    const u64 mu = (mu_full >> 64) ? ~0ull : (u64)mu_full;
+    return BarrettQ{q, (u64)r, (u64)(r >> 64), mu, ~0ull / q, sh, 0};
 }
 
 inline bool miller_rabin(u64 n) {

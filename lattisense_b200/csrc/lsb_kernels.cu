@@ -104,11 +104,11 @@ __global__ void __launch_bounds__(kElemThreads) k_tensor(const __grid_constant__
         Acc128 t{0, 0};
         acc_mad(t, a0.a, b1.a);
         acc_mad(t, a1.a, b0.a);
-        c1.a = barrett128(t.lo, t.hi, bq);
+        c1.a = reduce_wide(t.lo, t.hi, bq);  // 2 q^2 < 2^(sh+64) for q < 2^62
         Acc128 u{0, 0};
         acc_mad(u, a0.b, b1.b);
         acc_mad(u, a1.b, b0.b);
-        c1.b = barrett128(u.lo, u.hi, bq);
+        c1.b = reduce_wide(u.lo, u.hi, bq);
     }
     (void)q;
     st2(po + (size_t)i * N, j2, c0);
@@ -255,6 +255,7 @@ __global__ void __launch_bounds__(kElemThreads) k_ks_inner(const __grid_constant
     const u64* pext = a.ext.at(b);
     const u64* pc = a.cntt.at(b) + (size_t)a.cntt_slot0 * N;
     Acc128 s0a{0, 0}, s0b{0, 0}, s1a{0, 0}, s1b{0, 0};
+    int terms = 0;
     for (int d = 0; d < a.beta; d++) {
         const bool own = t < a.l && t >= d * a.alpha && t < (d + 1) * a.alpha;
         const W2 x = own ? ld2(pc + (size_t)t * N, j2) : ld2(pext + (size_t)(d * lk + t) * N, j2);
@@ -264,12 +265,20 @@ __global__ void __launch_bounds__(kElemThreads) k_ks_inner(const __grid_constant
         acc_mad(s0b, x.b, e0.b);
         acc_mad(s1a, x.a, e1.a);
         acc_mad(s1b, x.b, e1.b);
+        // reduce_wide needs the sum below 2^(sh+64): fold after `fold` products (61-bit primes with beta > 4 only)
+        if (++terms == a.fold && d + 1 < a.beta) {
+            s0a = Acc128{reduce_wide(s0a.lo, s0a.hi, bq), 0};
+            s0b = Acc128{reduce_wide(s0b.lo, s0b.hi, bq), 0};
+            s1a = Acc128{reduce_wide(s1a.lo, s1a.hi, bq), 0};
+            s1b = Acc128{reduce_wide(s1b.lo, s1b.hi, bq), 0};
+            terms = 1;
+        }
     }
     W2 o0, o1;
-    o0.a = barrett128(s0a.lo, s0a.hi, bq);
-    o0.b = barrett128(s0b.lo, s0b.hi, bq);
-    o1.a = barrett128(s1a.lo, s1a.hi, bq);
-    o1.b = barrett128(s1b.lo, s1b.hi, bq);
+    o0.a = reduce_wide(s0a.lo, s0a.hi, bq);
+    o0.b = reduce_wide(s0b.lo, s0b.hi, bq);
+    o1.a = reduce_wide(s1a.lo, s1a.hi, bq);
+    o1.b = reduce_wide(s1b.lo, s1b.hi, bq);
     u64* pacc = a.acc.at(b);
     st2(pacc + (size_t)t * N, j2, o0);
     st2(pacc + (size_t)(lk + t) * N, j2, o1);
@@ -300,7 +309,7 @@ __global__ void __launch_bounds__(kElemThreads) k_rescale_lift(const __grid_cons
     u64* pt = g.tmp.at(b) + (size_t)p * g.level * g.N;
     for (int i = 0; i < g.level; i++) {
         const ModConst& m = g.mods[i];
-        const u64 hq = barrett64(half, m.bq);
+        const u64 hq = barrett64(half, m.bq);  // CTA-uniform
         W2 o;
         o.a = submod(barrett64(x.a, m.bq), hq, m.q);
         o.b = submod(barrett64(x.b, m.bq), hq, m.q);

@@ -15,6 +15,11 @@ struct DeviceTables {
     const Tw* tw_inv = nullptr;  // [nmod][N]  psi^-bitrev(i)
     const TwD* tw_fwd_d = nullptr;  // FP64 policy: (w, w/q) pairs, zero for ineligible primes
     const TwD* tw_inv_d = nullptr;
+    // the same tables with the stages of the cluster kernel's last round in tail-SoA order (lsb_ntt_arith.h)
+    const Tw* twc_fwd = nullptr;
+    const Tw* twc_inv = nullptr;
+    const TwD* twc_fwd_d = nullptr;
+    const TwD* twc_inv_d = nullptr;
     const ModConst* mods = nullptr;
     Profiler* prof = nullptr;
     std::vector<uint8_t> f64_ok;  // host copy: modulus qualifies for the FP64 butterfly policy
@@ -39,6 +44,7 @@ enum BexMode {
 struct BexJob {
     int ns, nt, mode;
     int centered;  // ns == 1 in key-switch ModUp: centred lift instead of the CRT formula
+    int wide_ok;   // ns * max(source modulus) < 2^63: the CRT sums fit reduce_wide (else two-word Barrett)
     uint8_t src_slot[kBexMaxSrc], src_mod[kBexMaxSrc];
     uint8_t dst_slot[kBexMaxDst], dst_mod[kBexMaxDst], other_slot[kBexMaxDst];
     Tw qhat_inv[kBexMaxSrc];
@@ -82,6 +88,7 @@ struct KsInnerArgs {
     BatchPtr acc;    // [2][l+k]
     int l, k, beta, alpha, key_level;
     int nq;  // modulus index of P_0
+    int fold;  // products that may be accumulated before a reduction: fold * max(q) < 2^63 (reduce_wide bound)
 };
 void launch_ks_inner(const DeviceTables& dt, const KsInnerArgs& a, int batch, cudaStream_t s);
 

@@ -51,6 +51,9 @@ LSB_HD u64 negmod(u64 a, u64 q) { return a ? q - a : 0; }
 struct BarrettQ {
     u64 q;
     u64 r_lo, r_hi;
+    // shift-Barrett (reduce_wide): sh = bitlen(q) - 1, mu = floor(2^(sh+64) / q) < 2^64; qinv64 = floor((2^64-1)/q)
+    u64 mu, qinv64;
+    u32 sh, pad_;
 };
 
 // z = (hi:lo) < 2^128, returns z mod q (SEAL-style two-word Barrett; one correction).
@@ -67,17 +70,23 @@ LSB_HD u64 barrett128(u64 lo, u64 hi, const BarrettQ& m) {
     u64 rem = lo - quot * m.q;
     return csub(rem, m.q);
 }
-LSB_HD u64 barrett64(u64 x, const BarrettQ& m) {
-    // floor(x * r / 2^128) = hi64(x * r_hi + hi64(x * r_lo))
-    u64 c = umulhi(x, m.r_lo);
-    u64 lo = x * m.r_hi;
-    u64 hi = umulhi(x, m.r_hi);
-    u64 s = lo + c;
-    hi += (s < c);
-    u64 rem = x - hi * m.q;
-    return csub(rem, m.q);
+// x = (hi:lo) < 2^(sh+64) -> x mod q with one mul.hi and one mul.lo (the integer multiply pipe is what bounds the
+// element-wise kernels on B200: profiles/r01_elem_ncu_summary.txt).  With t = floor(x / 2^sh) < 2^64 and
+// qh = floor(t * mu / 2^64):  0 <= x/q - qh < 3, so x - qh*q < 3q < 2^64 and two conditional subtractions finish.
+// The bound covers any product of two values below 2q, and sums of n products of residues while n*q < 2^63.
+LSB_HD u64 reduce_wide(u64 lo, u64 hi, const BarrettQ& m) {
+    const u64 t = (hi << (64 - m.sh)) | (lo >> m.sh);
+    const u64 qh = umulhi(t, m.mu);
+    u64 r = lo - qh * m.q;
+    r = csub(r, m.q << 1);
+    return csub(r, m.q);
 }
-LSB_HD u64 mulmod(u64 a, u64 b, const BarrettQ& m) { return barrett128(a * b, umulhi(a, b), m); }
+// any 64-bit x -> x mod q
+LSB_HD u64 barrett64(u64 x, const BarrettQ& m) {
+    u64 r = x - umulhi(x, m.qinv64) * m.q;  // [0, 2q)
+    return csub(r, m.q);
+}
+LSB_HD u64 mulmod(u64 a, u64 b, const BarrettQ& m) { return reduce_wide(a * b, umulhi(a, b), m); }
 
 // 128-bit accumulator for lazy inner products.
 struct Acc128 {

@@ -146,7 +146,18 @@ struct ArithF64 {
 
 // LR consecutive forward stages on R = 2^LR values; tbase = twiddle index of the round's first stage for
 // this group (see lsb_ntt_core.h)
-template <class P, int LR>
+//
+// S1 >= 0 selects the "tail-SoA" table layout (host::soa_tail in lsb_tables.h) used by the contiguous last round of
+// the cluster NTT, whose first global stage is S1: there every thread has its own tbase, and in the standard
+// bit-reversed layout a warp's load of twiddle (r, kg) touches addresses 2^r * 16 bytes apart (up to 32
+// wavefronts per load).  In the SoA layout entry (r, kg) of group tl = tbase - 2^S1 lives at
+// ((2^r | kg) << S1) + tl, so consecutive lanes read consecutive 16-byte entries (4 wavefronts per load).
+template <int S1>
+LSB_HD u32 tw_index(u32 tbase, int r, int kg) {
+    if (S1 >= 0) return ((((u32)1 << r) | (u32)kg) << (S1 >= 0 ? S1 : 0)) + (tbase - ((u32)1 << (S1 >= 0 ? S1 : 0)));
+    return (tbase << r) | (u32)kg;
+}
+template <class P, int LR, int S1 = -1>
 LSB_HD void fwd_stages(typename P::V (&x)[1 << LR], const typename P::TW* __restrict__ tw, u32 tbase, const ModCtx& m) {
     constexpr int R = 1 << LR;
 #pragma unroll
@@ -154,14 +165,14 @@ LSB_HD void fwd_stages(typename P::V (&x)[1 << LR], const typename P::TW* __rest
         const int hk = R >> (r + 1);
 #pragma unroll
         for (int kg = 0; kg < (1 << r); kg++) {
-            const typename P::TW t = tw[(tbase << r) | (u32)kg];
+            const typename P::TW t = tw[tw_index<S1>(tbase, r, kg)];
 #pragma unroll
             for (int i = 0; i < hk; i++) P::ct(x[kg * 2 * hk + i], x[kg * 2 * hk + i + hk], t, m);
         }
     }
 }
 // the same stages inverted (Gentleman-Sande, last stage first).  FINAL: the round contains global stage 0.
-template <class P, int LR, bool FINAL>
+template <class P, int LR, bool FINAL, int S1 = -1>
 LSB_HD void inv_stages(typename P::V (&x)[1 << LR], const typename P::TW* __restrict__ tw, u32 tbase, const ModCtx& m,
                        typename P::TW ninv, typename P::TW w_ninv) {
     constexpr int R = 1 << LR;
@@ -174,7 +185,7 @@ LSB_HD void inv_stages(typename P::V (&x)[1 << LR], const typename P::TW* __rest
         } else {
 #pragma unroll
             for (int kg = 0; kg < (1 << r); kg++) {
-                const typename P::TW t = tw[(tbase << r) | (u32)kg];
+                const typename P::TW t = tw[tw_index<S1>(tbase, r, kg)];
 #pragma unroll
                 for (int i = 0; i < hk; i++) P::gs(x[kg * 2 * hk + i], x[kg * 2 * hk + i + hk], t, m);
             }

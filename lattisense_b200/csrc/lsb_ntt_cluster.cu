@@ -114,8 +114,8 @@ __global__ void __launch_bounds__(ClusterCfg<LOGN>::NT, LSB_CL_MINB) k_ntt_clust
             constexpr int GPB = BS >> lr;  // groups per block
             for (int gg = tid; gg < NB * GPB; gg += NT) {
                 const int st = gg / GPB, g = gg - st * GPB;
-                local_round<P, lr, false, false, last>(sm + st * BS, tw, g, loggc, PL.rounds[i].v, 16u + (u32)(rank * NB + st), m,
-                                                       nullptr, nullptr);
+                local_round<P, lr, false, false, last, (last ? LOGN - lr : -1)>(sm + st * BS, tw, g, loggc, PL.rounds[i].v,
+                                                                                16u + (u32)(rank * NB + st), m, nullptr, nullptr);
             }
             __syncthreads();
         });
@@ -130,8 +130,9 @@ __global__ void __launch_bounds__(ClusterCfg<LOGN>::NT, LSB_CL_MINB) k_ntt_clust
             constexpr int GPB = BS >> lr;
             for (int gg = tid; gg < NB * GPB; gg += NT) {
                 const int st = gg / GPB, g = gg - st * GPB;
-                local_round<P, lr, true, first, false>(sm + st * BS, tw, g, loggc, PL.rounds[i].v, 16u + (u32)(rank * NB + st), m,
-                                                       src + (size_t)rank * TILE + st * BS);
+                local_round<P, lr, true, first, false, (first ? LOGN - lr : -1)>(sm + st * BS, tw, g, loggc, PL.rounds[i].v,
+                                                                                 16u + (u32)(rank * NB + st), m,
+                                                                                 src + (size_t)rank * TILE + st * BS);
             }
             __syncthreads();
         });
@@ -213,8 +214,8 @@ void launch_ntt_cluster(const DeviceTables& dt, BatchPtr in, BatchPtr out, const
         a.in = in;
         a.out = out;
         a.total_rows = batch * parts[f].n;
-        a.tw = inverse ? dt.tw_inv : dt.tw_fwd;
-        a.tw_d = inverse ? dt.tw_inv_d : dt.tw_fwd_d;
+        a.tw = inverse ? dt.twc_inv : dt.twc_fwd;  // tail-SoA copies (host::soa_tail)
+        a.tw_d = inverse ? dt.twc_inv_d : dt.twc_fwd_d;
         a.mods = dt.mods;
         a.map = parts[f];
         ProfScope _ps(dt.prof, inverse ? PK_NTT_INV : PK_NTT_FWD, s, 16.0 * dt.N * a.total_rows, 1);

@@ -5,12 +5,19 @@
 
 namespace lsb {
 
+// radix (log2) of the contiguous last local round of the cluster transform for ring degree 2^logN
+LSB_HD constexpr int cluster_last_lr(int logN) {
+    const Plan p = make_plan(logN - 4, 0);
+    return p.rounds[p.nrounds - 1].lr;
+}
+
 // one local round on sub-tile `smt` (BS words, swizzled): LR stages starting at local stage v.
 // RAW_SRC (first inverse round): canonical residues are read straight from global memory `gsrc` (block base);
 // CANON (last forward round): canonical residues are written to global memory `gdst` if given (measured
 // slower than staging through shared memory on B200: half-sector stores), else to shared memory.  Both only
 // occur in the contiguous round (logGC == 0), where a thread owns 2^LR consecutive words.
-template <class P, int LR, bool INV, bool RAW_SRC, bool CANON>
+// S1 >= 0: tail-SoA twiddle layout (lsb_ntt_arith.h), only valid for the contiguous round whose first global stage is S1.
+template <class P, int LR, bool INV, bool RAW_SRC, bool CANON, int S1 = -1>
 LSB_HD void local_round(u64* smt, const typename P::TW* __restrict__ tw, int g, int logGC, int v, u32 twbase,
                         const ModCtx& m, const u64* __restrict__ gsrc = nullptr, u64* __restrict__ gdst = nullptr) {
     constexpr int R = 1 << LR;
@@ -32,8 +39,8 @@ LSB_HD void local_round(u64* smt, const typename P::TW* __restrict__ tw, int g, 
         }
     }
     const u32 tbase = (twbase << v) + (u32)hi;
-    if (!INV) fwd_stages<P, LR>(x, tw, tbase, m);
-    else inv_stages<P, LR, false>(x, tw, tbase, m, typename P::TW{}, typename P::TW{});
+    if (!INV) fwd_stages<P, LR, S1>(x, tw, tbase, m);
+    else inv_stages<P, LR, false, S1>(x, tw, tbase, m, typename P::TW{}, typename P::TW{});
     if (logGC == 0) {
 #pragma unroll
         for (int k = 0; k < R; k += 2) {

@@ -108,6 +108,12 @@ static void ks_core(OpEnv& e, int level, BatchPtr c_coeff, int coeff_slot0, Batc
     ia.alpha = alpha;
     ia.key_level = key_level;
     ia.nq = c.nq;
+    {
+        u64 qmax = 0;
+        for (int i = 0; i < l; i++) qmax = std::max(qmax, c.moduli[i]);
+        for (int j = 0; j < k; j++) qmax = std::max(qmax, c.moduli[c.idxP(j)]);
+        ia.fold = (int)std::min<u64>(1u << 20, ((1ull << 63) - 1) / qmax);
+    }
     launch_ks_inner(dt, ia, nb, e.s);
     {
         RowMap m;

@@ -2,6 +2,7 @@
 // the CUDA context and by tests/emul).
 #pragma once
 #include <cstring>
+#include <vector>
 #include "lsb_kernels.h"
 #include "lsb_host_math.h"
 
@@ -46,6 +47,21 @@ inline void build_ntt_tables(u64 qq, int logN, Tw* f, Tw* iv, ModConst* mc, TwD*
         }
 }
 
+// Re-order the stages s1+1 .. logN-1 (s1 = logN - lrl, lrl = radix of the cluster kernel's contiguous last round)
+// of one modulus' bit-reversed twiddle table into the tail-SoA layout read through tw_index<S1> (lsb_ntt_arith.h):
+// entry (tl << r) | kg of stage s1 + r moves to kg * 2^s1 + tl.
+template <class T>
+inline void soa_tail(T* table, int logN, int lrl) {
+    const int s1 = logN - lrl;
+    std::vector<T> seg;
+    for (int r = 1; r < lrl; r++) {
+        const size_t base = (size_t)1 << (s1 + r), groups = (size_t)1 << s1;
+        seg.assign(table + base, table + 2 * base);
+        for (size_t tl = 0; tl < groups; tl++)
+            for (size_t kg = 0; kg < ((size_t)1 << r); kg++) table[base + kg * groups + tl] = seg[(tl << r) | kg];
+    }
+}
+
 // CRT tables for extending residues from the moduli `src` to each modulus of `dst` (indices into `moduli`).
 inline BexJob make_bex_tables(const std::vector<u64>& moduli, const std::vector<int>& src, const std::vector<int>& dst) {
     using namespace host;
@@ -55,6 +71,11 @@ inline BexJob make_bex_tables(const std::vector<u64>& moduli, const std::vector<
     j.ns = (int)src.size();
     j.nt = (int)dst.size();
     j.mode = BEX_PLAIN;
+    {
+        u64 smax = 0;
+        for (int i = 0; i < j.ns; i++) smax = std::max(smax, moduli[src[i]]);
+        j.wide_ok = ((u128)smax * (u128)j.ns < ((u128)1 << 63)) ? 1 : 0;
+    }
     for (int i = 0; i < j.ns; i++) {
         const u64 si = moduli[src[i]];
         j.src_mod[i] = (uint8_t)src[i];

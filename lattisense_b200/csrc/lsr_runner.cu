@@ -38,6 +38,8 @@ namespace lsr {
 using lsb::BatchPtr;
 using lsb::u64;
 
+void lsr_stream_copy(void* dst, const void* src, size_t bytes);  // lsr_hostcopy.cpp
+
 // ---------------------------------------------------------------------------------------------
 // host worker pool (EXPORT / IMPORT / custom nodes, staging copies)
 // ---------------------------------------------------------------------------------------------
@@ -104,6 +106,7 @@ struct PinnedRing {
         uint64_t ticket;
         size_t begin, end;
         cudaEvent_t ev;  // nullptr until committed
+        bool done;       // released by ticket (regions lent out as zero-copy C structs)
     };
     std::deque<Busy> busy;
     std::vector<cudaEvent_t> free_events;
@@ -135,14 +138,22 @@ struct PinnedRing {
         LSB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         return e;
     }
+    void drop_ticket(uint64_t ticket) {  // mu held
+        for (auto it = busy.begin(); it != busy.end(); ++it)
+            if (it->ticket == ticket) {
+                if (it->ev) free_events.push_back(it->ev);
+                busy.erase(it);
+                return;
+            }
+    }
     uint8_t* acquire(size_t bytes, uint64_t* ticket) {
         bytes = (bytes + 255) & ~(size_t)255;
         LSB_CHECK(bytes <= cap, "lsb runner: object larger than the pinned staging ring (raise LSB_STAGING_MB)");
         std::unique_lock<std::mutex> lk(mu);
         for (;;) {
             // drop finished regions from the front
-            while (!busy.empty() && busy.front().ev && cudaEventQuery(busy.front().ev) == cudaSuccess) {
-                free_events.push_back(busy.front().ev);
+            while (!busy.empty() && (busy.front().done || (busy.front().ev && cudaEventQuery(busy.front().ev) == cudaSuccess))) {
+                if (busy.front().ev) free_events.push_back(busy.front().ev);
                 busy.pop_front();
             }
             size_t at = head + bytes > cap ? 0 : head;
@@ -155,14 +166,24 @@ struct PinnedRing {
             if (!clash) {
                 head = at + bytes;
                 *ticket = next_ticket++;
-                busy.push_back(Busy{*ticket, at, at + bytes, nullptr});
+                busy.push_back(Busy{*ticket, at, at + bytes, nullptr, false});
                 return base + at;
             }
-            if (clash->ev) {
+            const uint64_t ct = clash->ticket;
+            if (clash->done) {
+                drop_ticket(ct);
+            } else if (clash->ev) {
                 cudaEvent_t ev = clash->ev;
                 lk.unlock();
                 LSB_CUDA(cudaEventSynchronize(ev));
                 lk.lock();
+                // the entry may not be at the front (regions finish out of order): drop it by ticket unless another
+                // thread already did and the event was recycled for a newer region
+                for (auto& b2 : busy)
+                    if (b2.ticket == ct && b2.ev == ev) {
+                        drop_ticket(ct);
+                        break;
+                    }
             } else {
                 cv.wait_for(lk, std::chrono::milliseconds(1));
             }
@@ -173,6 +194,15 @@ struct PinnedRing {
             std::lock_guard<std::mutex> lk(mu);
             for (auto& b : busy)
                 if (b.ticket == ticket) b.ev = ev;
+        }
+        cv.notify_all();
+    }
+    // the region is free again regardless of any event (its owner is done with the memory)
+    void release(uint64_t ticket) {
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            for (auto& b : busy)
+                if (b.ticket == ticket) b.done = true;
         }
         cv.notify_all();
     }
@@ -302,6 +332,7 @@ struct Unit {
     int priority = 0;
     int slot = 0;                          // device slot; -1: every device (key load)
     int component = -1;
+    int order_key = 0;                     // LOAD: id of the first GPU unit that consumes the object (-1: key)
 };
 
 struct Plan {
@@ -335,7 +366,7 @@ static ComputeNode* sole_consumer(const DatumNode* d, OperationType want) {
     return c->input_nodes[0] == d ? c : nullptr;
 }
 
-static Plan build_plan(TaskGraph& g, bool fuse) {
+static Plan build_plan(TaskGraph& g, bool fuse, bool fuse_host) {
     Plan p;
     p.total_nodes = g.computes.size();
     std::vector<NodeIndex> order;
@@ -360,6 +391,25 @@ static Plan build_plan(TaskGraph& g, bool fuse) {
             chains[m] = chain;
         }
     }
+    // pass 1b: host chains.  EXPORT_TO_ABI -> LOAD_TO_BACKEND and STORE_FROM_BACKEND -> IMPORT_FROM_ABI run back to
+    // back on one worker thread: the limbs EXPORT just wrote are still in that core's cache when LOAD stages them,
+    // and IMPORT reads the stored object straight out of the pinned staging region (no intermediate copy).
+    if (fuse_host) {
+        for (NodeIndex ci : order) {
+            ComputeNode* a = &g.computes.at(ci);
+            if (a->custom_prop.has_value() || !a->fhe_prop.has_value() || a->output_nodes.size() != 1) continue;
+            const OperationType op = op_of(a);
+            if (op != OperationType::EXPORT_TO_ABI && op != OperationType::STORE_FROM_BACKEND) continue;
+            const DatumNode* d = a->output_nodes[0];
+            if (d->is_output || d->is_input || d->successors.size() != 1) continue;
+            ComputeNode* b = d->successors[0];
+            if (b->custom_prop.has_value() || !b->fhe_prop.has_value() || b->input_nodes.size() != 1 || absorbed.count(b)) continue;
+            const OperationType want = op == OperationType::EXPORT_TO_ABI ? OperationType::LOAD_TO_BACKEND : OperationType::IMPORT_FROM_ABI;
+            if (op_of(b) != want) continue;
+            chains[a] = {a, b};
+            absorbed.insert(b);
+        }
+    }
     for (NodeIndex ci : order) {
         ComputeNode* c = &g.computes.at(ci);
         if (absorbed.count(c)) continue;
@@ -368,11 +418,11 @@ static Plan build_plan(TaskGraph& g, bool fuse) {
         auto it = chains.find(c);
         if (it != chains.end()) {
             u.nodes = it->second;
-            p.fused_nodes += (long long)u.nodes.size() - 1;
+            if (is_device_op(c)) p.fused_nodes += (long long)u.nodes.size() - 1;
         } else {
             u.nodes = {c};
         }
-        const OperationType op = op_of(c);
+        const OperationType op = op_of(u.nodes.back()) == OperationType::LOAD_TO_BACKEND ? OperationType::LOAD_TO_BACKEND : op_of(c);
         if (op == OperationType::LOAD_TO_BACKEND) u.kind = UnitKind::LOAD;
         else if (op == OperationType::STORE_FROM_BACKEND) u.kind = UnitKind::STORE;
         else if (is_device_op(c)) u.kind = UnitKind::GPU;
@@ -395,6 +445,14 @@ static Plan build_plan(TaskGraph& g, bool fuse) {
     for (Unit& u : p.units) {
         for (DatumNode* in : u.ext_inputs) p.consumers[in->index].push_back(u.id);
         p.producer[u.output->index] = u.id;
+    }
+    for (Unit& u : p.units) {
+        if (u.kind != UnitKind::LOAD) continue;
+        const bool key = u.output->fhe_prop.has_value() && is_key_type(u.output->datum_type);
+        u.order_key = key ? -1 : (int)p.units.size();
+        auto it = p.consumers.find(u.output->index);
+        if (!key && it != p.consumers.end())
+            for (int v : it->second) u.order_key = std::min(u.order_key, v);
     }
     // components: units joined through non-key data (keys are shared by everything and replicated instead)
     std::vector<int> parent(p.units.size());
@@ -583,6 +641,10 @@ struct RunState {
     void dispatch();
 };
 
+// worker-pool priorities: results drain first, then input staging in consumer order, then other host nodes
+static const int kDrainPriority = 2000000;
+static const int kLoadPriority = 1000000;
+
 // ---- host nodes: EXPORT_TO_ABI, IMPORT_FROM_ABI, custom (cpu_task_utils.h:420-506) ----
 void RunState::run_host_unit(const Unit& u) {
     const ComputeNode& node = *u.nodes[0];
@@ -635,14 +697,23 @@ void collect_ksk(const CKeySwitchKey& k, LimbList& out) {
 }  // namespace
 
 void RunState::run_load_unit(const Unit& u) {
-    const ComputeNode& node = *u.nodes[0];
+    const ComputeNode& node = *u.nodes.back();
     std::any output;
     try {
         if (failed.load()) throw std::runtime_error("cancelled");
         const DatumNode* src = node.input_nodes[0];
         LSB_CHECK(src->fhe_prop.has_value(), "Input node missing FHE properties");
         auto in = gather_inputs(u);
-        const std::any& cs = in.at(src->index);
+        std::any exported;
+        if (u.nodes.size() == 2) {
+            // fused EXPORT_TO_ABI: run the bound executor here, on the thread that stages its result
+            const ComputeNode& ex = *u.nodes[0];
+            if (!ex.executor) throw std::runtime_error("lsb runner: no executor bound for node '" + ex.id + "'");
+            ExecutionContext ctx;
+            ctx.context = frontend_ctx;
+            ex.executor(ctx, in, exported, ex);
+        }
+        const std::any& cs = u.nodes.size() == 2 ? exported : in.at(src->index);
         LimbList ll;
         std::shared_ptr<void> keepalive;
         switch (src->datum_type) {
@@ -704,7 +775,7 @@ void RunState::run_load_unit(const Unit& u) {
             LSB_CUDA(cudaSetDevice(rt->device));
             uint64_t ticket = 0;
             uint8_t* stage = rt->up.acquire(words * 8, &ticket);
-            for (size_t i = 0; i < ll.limbs.size(); i++) std::memcpy(stage + i * (size_t)ll.n * 8, ll.limbs[i], (size_t)ll.n * 8);
+            for (size_t i = 0; i < ll.limbs.size(); i++) lsr_stream_copy(stage + i * (size_t)ll.n * 8, ll.limbs[i], (size_t)ll.n * 8);
             cudaEvent_t ring_ev = rt->up.new_event();
             DevObjPtr obj;
             {
@@ -747,7 +818,6 @@ void RunState::start_store_unit(const Unit& u) {
         LSB_CUDA(cudaSetDevice(rt->device));
         uint64_t ticket = 0;
         uint8_t* stage = rt->down.acquire(obj->words * 8, &ticket);
-        cudaEvent_t ring_ev = rt->down.new_event();
         cudaEvent_t done_ev;
         LSB_CUDA(cudaEventCreateWithFlags(&done_ev, cudaEventDisableTiming));
         {
@@ -764,29 +834,60 @@ void RunState::start_store_unit(const Unit& u) {
             in_flight++;
         }
         const Unit* up = &u;
-        pool.submit(u.priority, [this, up, obj, rt, stage, ticket, ring_ev, done_ev] {
+        // results drain ahead of further input staging
+        pool.submit(kDrainPriority + u.priority, [this, up, obj, rt, stage, ticket, done_ev] {
             std::any output;
+            const int n = g.param.n;
             try {
                 LSB_CUDA(cudaSetDevice(rt->device));
                 LSB_CUDA(cudaEventSynchronize(done_ev));
-                const int n = g.param.n;
-                CCiphertext* c = (CCiphertext*)malloc(sizeof(CCiphertext));
-                alloc_ciphertext(c, obj->npoly - 1, obj->level, n);
-                std::shared_ptr<CCiphertext> sp(c, [](CCiphertext* p) {
-                    free_ciphertext(p);
-                    free(p);
-                });
-                size_t k = 0;
-                for (int pi = 0; pi < obj->npoly; pi++)
-                    for (int li = 0; li <= obj->level; li++, k++)
-                        std::memcpy(c->polys[pi].components[li].data, stage + k * (size_t)n * 8, (size_t)n * 8);
-                output = sp;
+                if (up->nodes.size() == 2) {
+                    // fused IMPORT_FROM_ABI: hand the bound executor a CCiphertext whose limbs ARE the pinned staging
+                    // region (valid for the duration of the call; the struct is owned by the runner, wrapper.h ownership
+                    // rules are unchanged for the caller's handles)
+                    const ComputeNode& imp = *up->nodes[1];
+                    if (!imp.executor) throw std::runtime_error("lsb runner: no executor bound for node '" + imp.id + "'");
+                    CCiphertext view;
+                    view.level = obj->level;
+                    view.degree = obj->npoly - 1;
+                    std::vector<CPolynomial> polys(obj->npoly);
+                    std::vector<CComponent> comps((size_t)obj->npoly * (obj->level + 1));
+                    size_t k = 0;
+                    for (int pi = 0; pi < obj->npoly; pi++) {
+                        polys[pi].n_component = obj->level + 1;
+                        polys[pi].components = &comps[k];
+                        for (int li = 0; li <= obj->level; li++, k++) {
+                            comps[k].n = n;
+                            comps[k].data = reinterpret_cast<uint64_t*>(stage + k * (size_t)n * 8);
+                        }
+                    }
+                    view.polys = polys.data();
+                    std::unordered_map<NodeIndex, std::any> in;
+                    in[imp.input_nodes[0]->index] = std::shared_ptr<CCiphertext>(&view, [](CCiphertext*) {});
+                    ExecutionContext ctx;
+                    ctx.context = frontend_ctx;
+                    auto it = output_handles.find(up->output->index);
+                    if (it != output_handles.end()) ctx.other_args.push_back(std::any(it->second));
+                    imp.executor(ctx, in, output, imp);
+                } else {
+                    CCiphertext* c = (CCiphertext*)malloc(sizeof(CCiphertext));
+                    alloc_ciphertext(c, obj->npoly - 1, obj->level, n);
+                    std::shared_ptr<CCiphertext> sp(c, [](CCiphertext* p) {
+                        free_ciphertext(p);
+                        free(p);
+                    });
+                    size_t k = 0;
+                    for (int pi = 0; pi < obj->npoly; pi++)
+                        for (int li = 0; li <= obj->level; li++, k++)
+                            std::memcpy(c->polys[pi].components[li].data, stage + k * (size_t)n * 8, (size_t)n * 8);
+                    output = sp;
+                }
             } catch (const std::exception& e) {
-                fail("node '" + up->nodes[0]->id + "': " + e.what());
+                fail("node '" + up->nodes.back()->id + "': " + e.what());
+            } catch (...) {
+                fail("node '" + up->nodes.back()->id + "': unknown exception");
             }
-            // the staging region is free again: hand the ring an already-completed event
-            cudaEventRecord(ring_ev, rt->d2h);
-            rt->down.commit(ticket, ring_ev);
+            rt->down.release(ticket);  // the staging region is free again
             cudaEventDestroy(done_ev);
             unit_done(*up, std::move(output), true);
         });
@@ -1142,8 +1243,8 @@ void RunState::flush_gpu(std::vector<int>& pending) {
 // ---------------------------------------------------------------------------------------------
 void RunState::dispatch() {
     const size_t total_units = plan.units.size();
-    const size_t batch_min = env_mb("LSB_BATCH_MIN", 256);
-    const auto linger = std::chrono::microseconds(env_mb("LSB_BATCH_LINGER_US", 300));
+    const size_t batch_min = env_mb("LSB_BATCH_MIN", 128);
+    const auto linger = std::chrono::microseconds(env_mb("LSB_BATCH_LINGER_US", 1000));
     std::vector<int> gpu_pending;
     auto pending_since = std::chrono::steady_clock::now();
     for (;;) {
@@ -1173,8 +1274,12 @@ void RunState::dispatch() {
                         in_flight++;
                     }
                     const Unit* up = &u;
-                    if (u.kind == UnitKind::HOST) pool.submit(u.priority, [this, up] { run_host_unit(*up); });
-                    else pool.submit(u.priority, [this, up] { run_load_unit(*up); });
+                    if (u.kind == UnitKind::HOST) {
+                        const bool drain = op_of(u.nodes[0]) == OperationType::IMPORT_FROM_ABI;
+                        pool.submit((drain ? kDrainPriority : 0) + u.priority, [this, up] { run_host_unit(*up); });
+                    } else {
+                        pool.submit(kLoadPriority - std::min(u.order_key, kLoadPriority - 1), [this, up] { run_load_unit(*up); });
+                    }
                     break;
                 }
                 case UnitKind::STORE: start_store_unit(u); break;
@@ -1292,7 +1397,8 @@ fhe_task_handle create_fhe_gpu_task(const char* project_path) {
     std::unique_ptr<GpuTask> t(new GpuTask());
     t->graph.reset(lsr::TaskGraph::load(std::string(project_path) + "/mega_ag.json"));
     const char* nofuse = getenv("LSB_NO_FUSE");
-    t->plan = lsr::build_plan(*t->graph, !(nofuse && atoi(nofuse) != 0));
+    const char* nohost = getenv("LSB_NO_HOST_FUSE");
+    t->plan = lsr::build_plan(*t->graph, !(nofuse && atoi(nofuse) != 0), !(nohost && atoi(nohost) != 0));
     return reinterpret_cast<fhe_task_handle>(t.release());
 }
 

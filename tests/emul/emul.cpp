@@ -117,13 +117,27 @@ static void rows_pass(int logN, const Tw* tw, const ModConst& mc, u64* data, boo
 
 // mirrors k_ntt_cluster (lsb_ntt_cluster.cu): cross radix-16 round + local rounds per 1/16 block; the CTA
 // split is irrelevant on the CPU (blocks are independent), the index / twiddle / arithmetic code is the same
-template <class P, int LR, bool INV, bool RAW, bool CANON>
-static void local_all(int logN, int i_round, const Plan& PL, u64* sm, const typename P::TW* tw, const ModCtx& m, u64* gio) {
+template <class P, int LR, bool INV, bool RAW, bool CANON, int S1>
+static void local_all_s(int logN, int i_round, const Plan& PL, u64* sm, const typename P::TW* tw, const ModCtx& m, u64* gio) {
     const int BS = (1 << logN) / 16, GPB = BS >> LR, loggc = plan_loggc(PL, i_round);
     for (int blk = 0; blk < 16; blk++)
         for (int g = 0; g < GPB; g++)
-            local_round<P, LR, INV, RAW, CANON>(sm + blk * BS, tw, g, loggc, PL.rounds[i_round].v, 16u + (u32)blk, m, gio + blk * BS,
-                                                gio + blk * BS);
+            local_round<P, LR, INV, RAW, CANON, S1>(sm + blk * BS, tw, g, loggc, PL.rounds[i_round].v, 16u + (u32)blk, m,
+                                                    gio + blk * BS, gio + blk * BS);
+}
+// the contiguous last round (RAW for the inverse, CANON for the forward transform) reads the tail-SoA twiddle layout
+template <class P, int LR, bool INV, bool RAW, bool CANON>
+static void local_all(int logN, int i_round, const Plan& PL, u64* sm, const typename P::TW* tw, const ModCtx& m, u64* gio) {
+    if (!(RAW || CANON)) return local_all_s<P, LR, INV, RAW, CANON, -1>(logN, i_round, PL, sm, tw, m, gio);
+    switch (logN - LR) {
+        case 8: return local_all_s<P, LR, INV, RAW, CANON, 8>(logN, i_round, PL, sm, tw, m, gio);
+        case 9: return local_all_s<P, LR, INV, RAW, CANON, 9>(logN, i_round, PL, sm, tw, m, gio);
+        case 10: return local_all_s<P, LR, INV, RAW, CANON, 10>(logN, i_round, PL, sm, tw, m, gio);
+        case 11: return local_all_s<P, LR, INV, RAW, CANON, 11>(logN, i_round, PL, sm, tw, m, gio);
+        case 12: return local_all_s<P, LR, INV, RAW, CANON, 12>(logN, i_round, PL, sm, tw, m, gio);
+        case 13: return local_all_s<P, LR, INV, RAW, CANON, 13>(logN, i_round, PL, sm, tw, m, gio);
+        default: throw std::runtime_error("emul: unhandled last-round stage");
+    }
 }
 template <class P, bool INV>
 static void local_dyn(int logN, int i, const Plan& PL, u64* sm, const typename P::TW* tw, const ModCtx& m, bool raw, bool canon,
@@ -178,6 +192,11 @@ int emul_ntt_cluster(int logN, u64 q, u64* data, int inverse, int f64) {
         std::vector<TwD> fd(N), ivd(N);
         ModConst mc;
         build_ntt_tables(q, logN, f.data(), iv.data(), &mc, fd.data(), ivd.data());
+        const int lrl = cluster_last_lr(logN);
+        soa_tail(f.data(), logN, lrl);
+        soa_tail(iv.data(), logN, lrl);
+        soa_tail(fd.data(), logN, lrl);
+        soa_tail(ivd.data(), logN, lrl);
         if (f64) {
             if (!mc.f64_ok) return 2;
             cluster_ntt<ArithF64>(logN, inverse ? ivd.data() : fd.data(), mc, mc.ninv_d, mc.w_ninv_d, data, inverse != 0);
@@ -240,6 +259,7 @@ int emul_basis_extend(int logN, const u64* moduli, int nmod, const int* src, int
 
 // a*b mod q through the device Barrett path, and 128-bit accumulate path
 u64 emul_mulmod(u64 a, u64 b, u64 q) { return mulmod(a, b, host::make_barrett(q)); }
+u64 emul_reduce_wide(u64 lo, u64 hi, u64 q) { return reduce_wide(lo, hi, host::make_barrett(q)); }
 u64 emul_barrett64(u64 a, u64 q) { return barrett64(a, host::make_barrett(q)); }
 u64 emul_mul_shoup(u64 a, u64 w, u64 q) { return mul_shoup(a, host::make_tw(w, q), q); }
 

@@ -101,6 +101,21 @@ def test_barrett_and_shoup(emul):
             assert emul.emul_mulmod(a, b, q) == a * b % q
 
 
+def test_reduce_wide_up_to_its_bound(emul):
+    """shift-Barrett (lsb_math.h reduce_wide): exact for every x < 2^(bitlen(q)-1+64), i.e. sums of n products of
+    residues while n*q < 2^63 -- the bound the key-switch inner product and the CRT sums rely on"""
+    rng = np.random.default_rng(11)
+    for q in [R.CKKS_N14.q[0], R.CKKS_N14.q[1], R.CKKS_N14.p[0], R.BFV_N14.q[0], R.CKKS_BTP_N16.p[0], R.CKKS_BTP_N16.q[0], 65537]:
+        bound = 1 << (q.bit_length() - 1 + 64)
+        nmax = ((1 << 63) - 1) // q
+        xs = [0, q - 1, q, 2 * q, bound - 1, bound - q, min(nmax, 1 << 20) * (q - 1) ** 2]
+        xs += [int(rng.integers(0, 2 ** 62)) * int(rng.integers(0, 2 ** 62)) % bound for _ in range(3000)]
+        xs += [bound - 1 - int(rng.integers(0, 2 ** 40)) for _ in range(500)]
+        for x in xs:
+            assert x < bound
+            assert emul.emul_reduce_wide(x & (2 ** 64 - 1), x >> 64, q) == x % q, (q, x)
+
+
 @pytest.mark.parametrize("params", [R.CKKS_N12, R.CKKS_N13, R.CKKS_N14, R.BFV_N13, R.CKKS_BTP_N15, R.CKKS_BTP_N16],
                          ids=lambda p: p.name)
 def test_cluster_ntt_both_policies_match_oracle(emul, params):

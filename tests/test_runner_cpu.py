@@ -43,13 +43,22 @@ def _describe(case):
     return h, t, dict(zip(["computes", "data", "host", "load", "store", "gpu", "fused", "components"], list(out)))
 
 
-def test_bridge_nodes_cfg1():
+def test_bridge_nodes_cfg1(monkeypatch):
     # cfg1: 2 compute nodes, inputs x, y, rlk, one output:
     # + 3 EXPORT + 3 LOAD + 1 STORE + 1 IMPORT = 10 nodes; mult+relin fuse into one GPU unit
+    monkeypatch.setenv("LSB_NO_HOST_FUSE", "1")
     h, t, d = _describe("cfg1_bfv_mult")
     try:
         assert d["computes"] == 10
         assert (d["host"], d["load"], d["store"], d["gpu"], d["fused"]) == (4, 3, 1, 1, 1)
+    finally:
+        h.th_close(t)
+    # default plan: each EXPORT runs inside its LOAD unit and the IMPORT inside the STORE unit (host chains)
+    monkeypatch.delenv("LSB_NO_HOST_FUSE")
+    h, t, d = _describe("cfg1_bfv_mult")
+    try:
+        assert d["computes"] == 10
+        assert (d["host"], d["load"], d["store"], d["gpu"], d["fused"]) == (0, 3, 1, 1, 1)
         assert d["data"] == 5 + 3 * 2 + 2
         assert d["components"] == 1
     finally:
@@ -78,7 +87,7 @@ def test_custom_node_splits_device_path():
         # + loaded again for the add; final output stored + imported
         assert d["gpu"] == 2 and d["fused"] == 1
         assert d["store"] == 2 and d["load"] == 4
-        assert d["host"] == 4 + 1 + 2  # 4 exports, 1 custom, 2 imports
+        assert d["host"] == 1  # the custom node; the 4 exports / 2 imports run inside their LOAD / STORE units
     finally:
         h.th_close(t)
 

@@ -110,7 +110,13 @@ Context::~Context() {
 
 // CRT tables for extending residues from the moduli `src` to each modulus of `dst`.
 BexJob Context::make_bex(const std::vector<int>& src, const std::vector<int>& dst) const {
-    return make_bex_tables(moduli, src, dst);
+    BexJob j = make_bex_tables(moduli, src, dst);
+    static const bool elem_f64 = [] {  // LSB_ELEM_F64=0: integer CRT everywhere (A/B switch)
+        const char* e = getenv("LSB_ELEM_F64");
+        return !(e && atoi(e) == 0);
+    }();
+    if (!elem_f64) j.f64_ok = 0;
+    return j;
 }
 
 static inline u64 ckey(int kind, int a, int b = 0, int c = 0) {
@@ -195,6 +201,7 @@ const FinishMap* Context::moddown_finish(int level, int addmask, int out_stride)
         }
     const void* d = to_device(&fm, sizeof(fm));
     cache_[key] = d;
+    fm_host_[d] = fm;
     return (const FinishMap*)d;
 }
 
@@ -222,7 +229,15 @@ const FinishMap* Context::rescale_finish(int level, int npoly) {
         }
     const void* d = to_device(&fm, sizeof(fm));
     cache_[key] = d;
+    fm_host_[d] = fm;
     return (const FinishMap*)d;
+}
+
+const FinishMap* Context::finish_host(const FinishMap* dev) {
+    std::lock_guard<std::mutex> lk(mu_);
+    auto it = fm_host_.find(dev);
+    LSB_CHECK(it != fm_host_.end(), "lsb: unknown finish map");
+    return &it->second;
 }
 
 const Tw* Context::qlinv(int level) {
@@ -306,6 +321,7 @@ const BexJob* Context::bfv_quant1_jobs(int level) {
             job.mulc[j] = make_tw(invmod(qprod, m), m);
             job.addc[j] = half.mod(m);
         }
+        bex_fill_f64(job, moduli);
         jobs.push_back(job);
     }
     const void* d = to_device(jobs.data(), jobs.size() * sizeof(BexJob));
@@ -338,6 +354,7 @@ const BexJob* Context::bfv_quant2_jobs(int level) {
             job.addc[i] = half.mod(qi);
             job.mulc[i] = make_tw(t % qi, qi);
         }
+        bex_fill_f64(job, moduli);
         jobs.push_back(job);
     }
     const void* d = to_device(jobs.data(), jobs.size() * sizeof(BexJob));

@@ -3,6 +3,7 @@
 // reconstructRNS with a float64 overflow count), restated in oracle/orc_core.hpp:139-202.
 #pragma once
 #include "lsb_kernels.h"
+#include "lsb_ntt_arith.h"
 
 namespace lsb {
 
@@ -19,6 +20,35 @@ LSB_HD void bex_coeff(const BexJob& job, const ModConst* mods, const u64* x, Oth
             const ModConst& m = mods[job.dst_mod[t]];
             u64 r = barrett64(c, m.bq);
             store(t, neg ? negmod(r, m.q) : r);
+        }
+        return;
+    }
+    if (job.f64_ok) {
+        // every modulus below 2^47: the same CRT on the FP64 pipe (the 64-bit integer multiplies of the path below
+        // are what bounds this kernel on B200).  y_i is brought to its canonical value first, so the float64
+        // overflow estimate sums exactly the terms Lattigo sums.
+        double yd[kBexMaxSrc];
+        double vf = 0.0;
+        for (int i = 0; i < job.ns; i++) {
+            const ModConst& ms = mods[job.src_mod[i]];
+            yd[i] = f64_canon_d(f64_mulmod(f64_from_u64(x[i]), job.qhat_inv_d[i], ms.qd), ms.qd, ms.qinvd);
+            vf += yd[i] / job.s_f64[i];
+        }
+        const int v = (int)(u64)vf;
+        for (int t = 0; t < job.nt; t++) {
+            const ModConst& m = mods[job.dst_mod[t]];
+            double acc = 0.0;  // |acc| <= 0.75 * ns * p < 2^51
+            for (int i = 0; i < job.ns; i++) acc = d_add(acc, f64_mulmod(yd[i], job.qhat_mod_d[t][i], m.qd));
+            acc = d_add(acc, -f64_from_u64(job.vS[t][v]));
+            if (job.mode == BEX_OTHER_SUB) {
+                const double e = f64_canon_d(acc, m.qd, m.qinvd);
+                const double d = d_add(f64_from_u64(other(t)), -e);
+                acc = d_add(f64_mulmod(d, job.mulc_d[t], m.qd), f64_from_u64(job.addc[t]));
+            } else if (job.mode == BEX_SUB_MUL) {
+                const double e = f64_canon_d(acc, m.qd, m.qinvd);
+                acc = f64_mulmod(d_add(e, -f64_from_u64(job.addc[t])), job.mulc_d[t], m.qd);
+            }
+            store(t, f64_canon_u(acc, m.qd, m.qinvd));
         }
         return;
     }

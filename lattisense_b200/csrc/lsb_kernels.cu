@@ -6,6 +6,7 @@
 // :177-227 (multiply), :229-238 (relinearize), :240-248 (rescale), :264-292 (rotations).
 #include "lsb_elem_core.h"
 #include "lsb_ntt_core.h"  // W2
+#include "lsb_ntt_arith.h"
 
 namespace lsb {
 
@@ -243,6 +244,7 @@ struct KsInnerK {
     int N;
     const ModConst* mods;
 };
+template <bool F64>
 __global__ void __launch_bounds__(kElemThreads) k_ks_inner(const __grid_constant__ KsInnerK g) {
     const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
     if (j2 >= g.N / 2) return;
@@ -250,10 +252,36 @@ __global__ void __launch_bounds__(kElemThreads) k_ks_inner(const __grid_constant
     const int t = blockIdx.y, b = blockIdx.z;
     const int lk = a.l + a.k, klimbs = a.key_level + 1 + a.k;
     const int key_limb = t < a.l ? t : a.key_level + 1 + (t - a.l);
-    const BarrettQ bq = g.mods[t < a.l ? t : a.nq + (t - a.l)].bq;
+    const ModConst& mc = g.mods[t < a.l ? t : a.nq + (t - a.l)];
     const size_t N = g.N;
     const u64* pext = a.ext.at(b);
     const u64* pc = a.cntt.at(b) + (size_t)a.cntt_slot0 * N;
+    u64* pacc = a.acc.at(b);
+    if constexpr (F64) {
+        // all primes below 2^47: products and sums on the FP64 pipe (|sum| <= 1.5 * beta * q < 2^51)
+        const double q = mc.qd, qinv = mc.qinvd;
+        double s0a = 0.0, s0b = 0.0, s1a = 0.0, s1b = 0.0;
+        for (int d = 0; d < a.beta; d++) {
+            const bool own = t < a.l && t >= d * a.alpha && t < (d + 1) * a.alpha;
+            const W2 x = own ? ld2(pc + (size_t)t * N, j2) : ld2(pext + (size_t)(d * lk + t) * N, j2);
+            const W2 e0 = ld2(a.evk + ((size_t)(d * 2 + 0) * klimbs + key_limb) * N, j2);
+            const W2 e1 = ld2(a.evk + ((size_t)(d * 2 + 1) * klimbs + key_limb) * N, j2);
+            const double xa = f64_from_u64(x.a), xb = f64_from_u64(x.b);
+            s0a = d_add(s0a, f64_mulmod_var(xa, f64_from_u64(e0.a), q, qinv));
+            s0b = d_add(s0b, f64_mulmod_var(xb, f64_from_u64(e0.b), q, qinv));
+            s1a = d_add(s1a, f64_mulmod_var(xa, f64_from_u64(e1.a), q, qinv));
+            s1b = d_add(s1b, f64_mulmod_var(xb, f64_from_u64(e1.b), q, qinv));
+        }
+        W2 o0, o1;
+        o0.a = f64_canon_u(s0a, q, qinv);
+        o0.b = f64_canon_u(s0b, q, qinv);
+        o1.a = f64_canon_u(s1a, q, qinv);
+        o1.b = f64_canon_u(s1b, q, qinv);
+        st2(pacc + (size_t)t * N, j2, o0);
+        st2(pacc + (size_t)(lk + t) * N, j2, o1);
+        return;
+    }
+    const BarrettQ bq = mc.bq;
     Acc128 s0a{0, 0}, s0b{0, 0}, s1a{0, 0}, s1b{0, 0};
     int terms = 0;
     for (int d = 0; d < a.beta; d++) {
@@ -279,7 +307,6 @@ __global__ void __launch_bounds__(kElemThreads) k_ks_inner(const __grid_constant
     o0.b = reduce_wide(s0b.lo, s0b.hi, bq);
     o1.a = reduce_wide(s1a.lo, s1a.hi, bq);
     o1.b = reduce_wide(s1b.lo, s1b.hi, bq);
-    u64* pacc = a.acc.at(b);
     st2(pacc + (size_t)t * N, j2, o0);
     st2(pacc + (size_t)(lk + t) * N, j2, o1);
 }
@@ -287,7 +314,8 @@ void launch_ks_inner(const DeviceTables& dt, const KsInnerArgs& a, int batch, cu
     if (batch <= 0) return;
     KsInnerK g{a, dt.N, dt.mods};
     ProfScope _ps(dt.prof, PK_KS_INNER, s, 8.0 * dt.N * (a.l + a.k) * (batch * (a.beta + 2.0) + 2.0 * a.beta));
-    k_ks_inner<<<elem_grid(dt.N, a.l + a.k, batch), kElemThreads, 0, s>>>(g);
+    if (a.f64 && a.beta <= 16) k_ks_inner<true><<<elem_grid(dt.N, a.l + a.k, batch), kElemThreads, 0, s>>>(g);
+    else k_ks_inner<false><<<elem_grid(dt.N, a.l + a.k, batch), kElemThreads, 0, s>>>(g);
     LSB_CUDA(cudaGetLastError());
 }
 

@@ -30,8 +30,9 @@ void launch_ntt(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap&
                 cudaStream_t s);
 
 // cluster kernel (lsb_ntt_cluster.cu); launch_ntt dispatches to it unless LSB_NTT_IMPL=single
+struct NttFinish;
 void launch_ntt_cluster(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap& map, int batch, bool inverse,
-                        const std::vector<uint8_t>& f64_ok, bool allow_f64, cudaStream_t s);
+                        const std::vector<uint8_t>& f64_ok, bool allow_f64, cudaStream_t s, const NttFinish* fin = nullptr);
 
 // ---- basis extension (ModUp / ModDown / BFV scaling), Lattigo-style with float64 overflow count ----
 constexpr int kBexMaxSrc = 16;
@@ -45,6 +46,7 @@ struct BexJob {
     int ns, nt, mode;
     int centered;  // ns == 1 in key-switch ModUp: centred lift instead of the CRT formula
     int wide_ok;   // ns * max(source modulus) < 2^63: the CRT sums fit reduce_wide (else two-word Barrett)
+    int f64_ok;    // every modulus involved is below 2^47: the CRT runs on the FP64 pipe (tables below)
     uint8_t src_slot[kBexMaxSrc], src_mod[kBexMaxSrc];
     uint8_t dst_slot[kBexMaxDst], dst_mod[kBexMaxDst], other_slot[kBexMaxDst];
     Tw qhat_inv[kBexMaxSrc];
@@ -53,6 +55,10 @@ struct BexJob {
     u64 vS[kBexMaxDst][kBexMaxSrc + 1];
     Tw mulc[kBexMaxDst];
     u64 addc[kBexMaxDst];
+    // FP64 copies (valid when f64_ok): (w, w/q) pairs with respect to the modulus the product is reduced by
+    TwD qhat_inv_d[kBexMaxSrc];
+    TwD qhat_mod_d[kBexMaxDst][kBexMaxSrc];
+    TwD mulc_d[kBexMaxDst];
 };
 // jobs: device array of njobs BexJob; src/dst/other: per-batch-item blocks.
 void launch_basis_extend(const DeviceTables& dt, const BexJob* jobs, int njobs, BatchPtr src, BatchPtr dst,
@@ -78,6 +84,15 @@ struct FinishMap {
 };
 void launch_finish(const DeviceTables& dt, BatchPtr a, BatchPtr b, BatchPtr addend, bool has_addend, BatchPtr out,
                    const FinishMap* fm_dev, int nrows, int batch, cudaStream_t s);
+// finish fused into the forward NTT that produces its `b` operand (cluster kernel epilogue): the transform of
+// b[fm.b_slot[r]] never goes to memory.  fm_host is the host copy of *fm_dev.
+struct NttFinish {
+    const FinishMap* fm_dev;
+    const FinishMap* fm_host;
+    BatchPtr a, addend, out;
+    bool has_addend;
+};
+void launch_ntt_finish(const DeviceTables& dt, BatchPtr b, const NttFinish& fin, int batch, cudaStream_t s);
 
 // key-switch inner product: acc[p][t] = sum_d D_d[t] * evk[d][p][keylimb(t)]
 struct KsInnerArgs {
@@ -88,6 +103,7 @@ struct KsInnerArgs {
     BatchPtr acc;    // [2][l+k]
     int l, k, beta, alpha, key_level;
     int nq;  // modulus index of P_0
+    int f64;   // every prime involved is below 2^47 (FP64-pipe variant)
     int fold;  // products that may be accumulated before a reduction: fold * max(q) < 2^63 (reduce_wide bound)
 };
 void launch_ks_inner(const DeviceTables& dt, const KsInnerArgs& a, int batch, cudaStream_t s);

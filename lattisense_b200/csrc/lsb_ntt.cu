@@ -243,6 +243,44 @@ static void launch_two_pass(NttArgs a, int sms, cudaStream_t s) {
     LSB_CUDA(cudaGetLastError());
 }
 
+static bool ntt_allow_f64() {
+    static const bool v = [] {
+        const char* e = getenv("LSB_NTT_F64");
+        return !(e && atoi(e) == 0);
+    }();
+    return v;
+}
+static bool ntt_use_cluster() {
+    static const bool v = [] {
+        const char* e = getenv("LSB_NTT_IMPL");
+        return !(e && std::string(e) == "single");
+    }();
+    return v;
+}
+
+// forward NTT of b[fm.b_slot[r]] + finish; with the cluster kernel the finish is its epilogue (LSB_NO_EPILOGUE=1: two launches)
+void launch_ntt_finish(const DeviceTables& dt, BatchPtr b, const NttFinish& fin, int batch, cudaStream_t s) {
+    const FinishMap& fm = *fin.fm_host;
+    if (batch <= 0 || fm.n <= 0) return;
+    static const bool fused = [] {
+        const char* e = getenv("LSB_NO_EPILOGUE");
+        return !(e && atoi(e) != 0);
+    }();
+    RowMap m;
+    m.n = fm.n;
+    for (int r = 0; r < fm.n; r++) {
+        m.in_slot[r] = fm.b_slot[r];
+        m.out_slot[r] = fused && ntt_use_cluster() ? (uint8_t)r : fm.b_slot[r];
+        m.mod[r] = fm.mod[r];
+    }
+    if (fused && ntt_use_cluster()) {
+        launch_ntt_cluster(dt, b, b, m, batch, false, dt.f64_ok, ntt_allow_f64(), s, &fin);
+        return;
+    }
+    launch_ntt(dt, b, b, m, batch, false, s);
+    launch_finish(dt, fin.a, b, fin.addend, fin.has_addend, fin.out, fin.fm_dev, fm.n, batch, s);
+}
+
 void launch_ntt(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap& map, int batch, bool inverse,
                 cudaStream_t s) {
     if (batch <= 0 || map.n <= 0) return;

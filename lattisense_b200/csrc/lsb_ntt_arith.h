@@ -86,6 +86,29 @@ LSB_HD double f64_centre(double v, double q, double qinv) {
     return d_fma(-qf, q, v);
 }
 
+// ---- FP64 modular arithmetic for the element-wise kernels (primes below 2^47, same exactness argument) ----
+// a * b mod q for two variable operands |a|, |b| < 2^48 (no precomputed b/q): the quotient estimate rint(h / q) may be
+// off by one, so |result| <= 1.5 q; h - qf*q is an integer below 2^50 and therefore exact in the FMA.
+LSB_HD double f64_mulmod_var(double a, double b, double q, double qinv) {
+    const double h = d_mul(a, b);
+    const double l = d_fma(a, b, -h);
+    const double qf = d_add(d_fma(h, qinv, kMagic), -kMagic);
+    return d_add(d_fma(-qf, q, h), l);
+}
+LSB_HD double f64_from_u64(u64 x) { return d_add(bits_to_double(x | 0x4330000000000000ull), -kTwo52); }  // x < 2^52
+// |v| < 2^51 -> canonical residue in [0, q) as a double / as an integer
+LSB_HD double f64_canon_d(double v, double q, double qinv) {
+    const double r = f64_centre(v, q, qinv);
+    return r < 0.0 ? d_add(r, q) : r;
+}
+LSB_HD u64 f64_canon_u(double v, double q, double qinv) {
+    const double r = f64_centre(v, q, qinv);
+    const double c = r < 0.0 ? d_add(q, kTwo52) : kTwo52;
+    return double_to_bits(d_add(r, c)) & 0x000FFFFFFFFFFFFFull;
+}
+// primes the element-wise FP64 paths accept (independent of the ring degree)
+constexpr u64 kElemF64Limit = 1ull << 47;
+
 struct ArithU64 {
     typedef u64 V;
     typedef Tw TW;

@@ -48,6 +48,11 @@ struct NttClArgs {
     const TwD* tw_d;  // [nmod][N]
     const ModConst* mods;
     RowMap map;
+    // fused finish epilogue (forward only): out[fm.out_slot[f]] = (fa[fm.a_slot[f]] - NTT(row)) * fm.c[f] (+ fadd[fm.add_slot[f]])
+    // with f = map.out_slot[row]; the transform itself is not stored
+    const FinishMap* fm;
+    BatchPtr fa, fadd, fout;
+    int has_add;
 };
 
 template <int I, int NR, class F>
@@ -64,7 +69,7 @@ __device__ __forceinline__ const typename P::TW* tw_of(const NttClArgs& a, int m
     else return a.tw + (size_t)mod * N;
 }
 
-template <int LOGN, bool INV, class P>
+template <int LOGN, bool INV, class P, bool FIN = false>
 __global__ void __launch_bounds__(ClusterCfg<LOGN>::NT, LSB_CL_MINB) k_ntt_cluster(const __grid_constant__ NttClArgs a) {
     typedef ClusterCfg<LOGN> C;
     extern __shared__ __align__(1024) u64 sm[];
@@ -119,8 +124,34 @@ __global__ void __launch_bounds__(ClusterCfg<LOGN>::NT, LSB_CL_MINB) k_ntt_clust
             }
             __syncthreads();
         });
-        u64* out = dst + (size_t)rank * TILE;
-        for (int c = tid; c < TILE / 2; c += NT) reinterpret_cast<W2*>(out)[c] = *reinterpret_cast<const W2*>(&sm[swz(2 * c)]);
+        if constexpr (!FIN) {
+            u64* out = dst + (size_t)rank * TILE;
+            for (int c = tid; c < TILE / 2; c += NT) reinterpret_cast<W2*>(out)[c] = *reinterpret_cast<const W2*>(&sm[swz(2 * c)]);
+        } else {
+            // ModDown / rescale finish on the integer pipe while other CTAs of the SM run FP64 butterflies
+            const int f = a.map.out_slot[r];
+            const FinishMap& fm = *a.fm;
+            const Tw cmul = fm.c[f];
+            const u64 q = mc.q;
+            const size_t off = (size_t)rank * (TILE / 2);
+            const W2* pa = reinterpret_cast<const W2*>(a.fa.at(b) + (size_t)fm.a_slot[f] * N) + off;
+            const bool add = a.has_add && fm.add_slot[f] != 0xFF;
+            const W2* pz = add ? reinterpret_cast<const W2*>(a.fadd.at(b) + (size_t)fm.add_slot[f] * N) + off : nullptr;
+            W2* po = reinterpret_cast<W2*>(a.fout.at(b) + (size_t)fm.out_slot[f] * N) + off;
+            for (int c = tid; c < TILE / 2; c += NT) {
+                const W2 y = *reinterpret_cast<const W2*>(&sm[swz(2 * c)]);
+                const W2 x = pa[c];
+                W2 o;
+                o.a = mul_shoup(submod(x.a, y.a, q), cmul, q);
+                o.b = mul_shoup(submod(x.b, y.b, q), cmul, q);
+                if (add) {
+                    const W2 z = pz[c];
+                    o.a = addmod(o.a, z.a, q);
+                    o.b = addmod(o.b, z.b, q);
+                }
+                po[c] = o;
+            }
+        }
     } else {
         static_for_cl<0, PL.nrounds>([&](auto ic) {
             constexpr int i = PL.nrounds - 1 - decltype(ic)::value;
@@ -161,13 +192,13 @@ __global__ void __launch_bounds__(ClusterCfg<LOGN>::NT, LSB_CL_MINB) k_ntt_clust
     }
 }
 
-template <int LOGN, bool INV, class P>
+template <int LOGN, bool INV, class P, bool FIN = false>
 static void launch_cluster_t(const NttClArgs& a, cudaStream_t s) {
     typedef ClusterCfg<LOGN> C;
     constexpr int smem = C::TILE * 8;
     static bool attr_done = false;
     if (!attr_done) {
-        LSB_CUDA(cudaFuncSetAttribute(k_ntt_cluster<LOGN, INV, P>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        LSB_CUDA(cudaFuncSetAttribute(k_ntt_cluster<LOGN, INV, P, FIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attr_done = true;
     }
     cudaLaunchConfig_t cfg = {};
@@ -182,11 +213,16 @@ static void launch_cluster_t(const NttClArgs& a, cudaStream_t s) {
     at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    LSB_CUDA(cudaLaunchKernelEx(&cfg, k_ntt_cluster<LOGN, INV, P>, a));
+    LSB_CUDA(cudaLaunchKernelEx(&cfg, k_ntt_cluster<LOGN, INV, P, FIN>, a));
 }
 
 template <int LOGN>
 static void launch_cluster_n(const NttClArgs& a, bool inverse, bool f64, cudaStream_t s) {
+    if (a.fm) {
+        if (f64) launch_cluster_t<LOGN, false, ArithF64, true>(a, s);
+        else launch_cluster_t<LOGN, false, ArithU64, true>(a, s);
+        return;
+    }
     if (f64) {
         if (inverse) launch_cluster_t<LOGN, true, ArithF64>(a, s);
         else launch_cluster_t<LOGN, false, ArithF64>(a, s);
@@ -198,7 +234,8 @@ static void launch_cluster_n(const NttClArgs& a, bool inverse, bool f64, cudaStr
 
 // Rows whose prime qualifies for the FP64 policy and the others go in separate launches (CTA-uniform code).
 void launch_ntt_cluster(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap& map, int batch, bool inverse,
-                        const std::vector<uint8_t>& f64_ok, bool allow_f64, cudaStream_t s) {
+                        const std::vector<uint8_t>& f64_ok, bool allow_f64, cudaStream_t s, const NttFinish* fin) {
+    LSB_CHECK(!(fin && inverse), "lsb: the finish epilogue belongs to the forward transform");
     RowMap parts[2];
     parts[0].n = parts[1].n = 0;
     for (int r = 0; r < map.n; r++) {
@@ -218,6 +255,16 @@ void launch_ntt_cluster(const DeviceTables& dt, BatchPtr in, BatchPtr out, const
         a.tw_d = inverse ? dt.twc_inv_d : dt.twc_fwd_d;
         a.mods = dt.mods;
         a.map = parts[f];
+        a.fm = fin ? fin->fm_dev : nullptr;
+        if (fin) {
+            a.fa = fin->a;
+            a.fadd = fin->addend;
+            a.fout = fin->out;
+            a.has_add = fin->has_addend ? 1 : 0;
+        } else {
+            a.fa = a.fadd = a.fout = in;
+            a.has_add = 0;
+        }
         ProfScope _ps(dt.prof, inverse ? PK_NTT_INV : PK_NTT_FWD, s, 16.0 * dt.N * a.total_rows, 1);
         switch (dt.logN) {
             case 12: launch_cluster_n<12>(a, inverse, f == 1, s); break;

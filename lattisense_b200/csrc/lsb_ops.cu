@@ -113,6 +113,11 @@ static void ks_core(OpEnv& e, int level, BatchPtr c_coeff, int coeff_slot0, Batc
         for (int i = 0; i < l; i++) qmax = std::max(qmax, c.moduli[i]);
         for (int j = 0; j < k; j++) qmax = std::max(qmax, c.moduli[c.idxP(j)]);
         ia.fold = (int)std::min<u64>(1u << 20, ((1ull << 63) - 1) / qmax);
+        static const bool elem_f64 = [] {
+            const char* e = getenv("LSB_ELEM_F64");
+            return !(e && atoi(e) == 0);
+        }();
+        ia.f64 = (elem_f64 && qmax < kElemF64Limit) ? 1 : 0;
     }
     launch_ks_inner(dt, ia, nb, e.s);
     {
@@ -127,8 +132,11 @@ static void ks_core(OpEnv& e, int level, BatchPtr c_coeff, int coeff_slot0, Batc
         launch_ntt(dt, acc, acc, m, nb, true, e.s);
     }
     launch_basis_extend(dt, c.moddown_jobs(level), 2, acc, md, md, nb, e.s);
-    launch_ntt(dt, md, md, rowmap_seq(2 * l, 0, 0, 0, l), nb, false, e.s);
-    launch_finish(dt, acc, md, addend, addmask != 0, res, c.moddown_finish(level, addmask, res_ps), 2 * l, nb, e.s);
+    {
+        const FinishMap* fm = c.moddown_finish(level, addmask, res_ps);
+        NttFinish fin{fm, c.finish_host(fm), acc, addend, res, addmask != 0};
+        launch_ntt_finish(dt, md, fin, nb, e.s);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -282,8 +290,11 @@ static void rescale_impl(OpEnv& e, int level, int npoly, BatchPtr in, BatchPtr o
     }
     launch_ntt(dt, in, last, m, nb, true, e.s);
     launch_rescale_lift(dt, last, 1, tmp, npoly, level, nb, e.s);
-    launch_ntt(dt, tmp, tmp, rowmap_seq(npoly * level, 0, 0, 0, level), nb, false, e.s);
-    launch_finish(dt, in, tmp, tmp, false, out, c.rescale_finish(level, npoly), npoly * level, nb, e.s);
+    {
+        const FinishMap* fm = c.rescale_finish(level, npoly);
+        NttFinish fin{fm, c.finish_host(fm), in, tmp, out, false};
+        launch_ntt_finish(dt, tmp, fin, nb, e.s);
+    }
 }
 void op_rescale(OpEnv& e, int level, int npoly, BatchPtr in, BatchPtr out, int batch) {
     LSB_CUDA(cudaSetDevice(e.c.device));

@@ -62,6 +62,20 @@ inline void soa_tail(T* table, int logN, int lrl) {
     }
 }
 
+// FP64 copies of a job's constants (call again after changing mulc): valid when every modulus is below 2^47
+inline void bex_fill_f64(BexJob& j, const std::vector<u64>& moduli) {
+    j.f64_ok = 1;
+    for (int i = 0; i < j.ns; i++) j.f64_ok &= moduli[j.src_mod[i]] < kElemF64Limit ? 1 : 0;
+    for (int t = 0; t < j.nt; t++) j.f64_ok &= moduli[j.dst_mod[t]] < kElemF64Limit ? 1 : 0;
+    if (!j.f64_ok) return;
+    for (int i = 0; i < j.ns; i++) j.qhat_inv_d[i] = make_twd(j.qhat_inv[i].w, moduli[j.src_mod[i]]);
+    for (int t = 0; t < j.nt; t++) {
+        const u64 p = moduli[j.dst_mod[t]];
+        for (int i = 0; i < j.ns; i++) j.qhat_mod_d[t][i] = make_twd(j.qhat_mod[t][i], p);
+        j.mulc_d[t] = make_twd(j.mulc[t].w, p);
+    }
+}
+
 // CRT tables for extending residues from the moduli `src` to each modulus of `dst` (indices into `moduli`).
 inline BexJob make_bex_tables(const std::vector<u64>& moduli, const std::vector<int>& src, const std::vector<int>& dst) {
     using namespace host;
@@ -98,6 +112,7 @@ inline BexJob make_bex_tables(const std::vector<u64>& moduli, const std::vector<
             j.qhat_mod[tt][i] = prod;
         }
     }
+    bex_fill_f64(j, moduli);
     return j;
 }
 

@@ -242,9 +242,12 @@ int emul_basis_extend(int logN, const u64* moduli, int nmod, const int* src, int
         for (int m = 0; m < nmod; m++) {
             mc[m].q = mods[m];
             mc[m].bq = host::make_barrett(mods[m]);
+            mc[m].qd = (double)mods[m];
+            mc[m].qinvd = 1.0 / (double)mods[m];
         }
         BexJob job = make_bex_tables(mods, std::vector<int>(src, src + ns), std::vector<int>(dst, dst + nt));
-        job.centered = centered;
+        job.centered = centered & 1;
+        if (centered & 2) job.f64_ok = 0;  // force the integer CRT (primes below 2^47 default to the FP64 one)
         for (int j = 0; j < N; j++) {
             u64 x[kBexMaxSrc];
             for (int i = 0; i < ns; i++) x[i] = in[(size_t)i * N + j];

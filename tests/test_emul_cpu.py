@@ -78,12 +78,13 @@ def test_basis_extend_matches_oracle(emul, params):
                 pj = o.moduli[d]
                 want[t] = np.array([(int(v) % pj) if int(v) < (s >> 1) else (-(s - int(v)) % pj) for v in xs],
                                    dtype=np.uint64)
-        got = np.zeros((len(dst), params.N), dtype=np.uint64)
         sa = (C.c_int * len(src))(*src)
         da = (C.c_int * len(dst))(*dst)
-        assert emul.emul_basis_extend(params.logN, R.P(mods), len(mods), sa, len(src), da, len(dst), centered,
-                                      R.P(x), R.P(got)) == 0
-        assert np.array_equal(got, want), (src, dst, centered)
+        for force_int in (0, 2):  # default policy (FP64 CRT when every prime is below 2^47), then the integer CRT
+            got = np.zeros((len(dst), params.N), dtype=np.uint64)
+            assert emul.emul_basis_extend(params.logN, R.P(mods), len(mods), sa, len(src), da, len(dst), centered | force_int,
+                                          R.P(x), R.P(got)) == 0
+            assert np.array_equal(got, want), (src, dst, centered, force_int)
 
 
 def test_barrett_and_shoup(emul):

@@ -119,6 +119,18 @@ BexJob Context::make_bex(const std::vector<int>& src, const std::vector<int>& ds
     return j;
 }
 
+const void* Context::upload_jobs(const std::vector<BexJob>& jobs) {  // mu_ held
+    const void* d = to_device(jobs.data(), jobs.size() * sizeof(BexJob));
+    std::vector<BexMeta>& m = bex_meta_[d];
+    for (const BexJob& j : jobs) m.push_back(BexMeta{j.ns, j.nt, j.mode, j.centered, j.f64_ok});
+    return d;
+}
+const BexMeta* Context::bex_meta(const BexJob* dev) {
+    std::lock_guard<std::mutex> lk(mu_);
+    auto it = bex_meta_.find(dev);
+    return it == bex_meta_.end() ? nullptr : it->second.data();
+}
+
 static inline u64 ckey(int kind, int a, int b = 0, int c = 0) {
     return ((u64)kind << 56) | ((u64)(a & 0xFFFFF) << 32) | ((u64)(b & 0xFFFF) << 16) | (u64)(c & 0xFFFF);
 }
@@ -150,7 +162,7 @@ const BexJob* Context::modup_jobs(int level, int coeff_slot0) {
         for (int tt = 0; tt < job.nt; tt++) job.dst_slot[tt] = (uint8_t)slots[tt];
         jobs.push_back(job);
     }
-    const void* d = to_device(jobs.data(), jobs.size() * sizeof(BexJob));
+    const void* d = upload_jobs(jobs);
     cache_[key] = d;
     return (const BexJob*)d;
 }
@@ -171,7 +183,7 @@ const BexJob* Context::moddown_jobs(int level) {
         for (int i = 0; i < l; i++) job.dst_slot[i] = (uint8_t)(p * l + i);
         jobs.push_back(job);
     }
-    const void* d = to_device(jobs.data(), jobs.size() * sizeof(BexJob));
+    const void* d = upload_jobs(jobs);
     cache_[key] = d;
     return (const BexJob*)d;
 }
@@ -288,7 +300,7 @@ const BexJob* Context::bfv_q_to_qmul_jobs(int level) {
         for (int j = 0; j < lm; j++) job.dst_slot[j] = (uint8_t)(p * L + l + j);
         jobs.push_back(job);
     }
-    const void* d = to_device(jobs.data(), jobs.size() * sizeof(BexJob));
+    const void* d = upload_jobs(jobs);
     cache_[key] = d;
     return (const BexJob*)d;
 }
@@ -324,7 +336,7 @@ const BexJob* Context::bfv_quant1_jobs(int level) {
         bex_fill_f64(job, moduli);
         jobs.push_back(job);
     }
-    const void* d = to_device(jobs.data(), jobs.size() * sizeof(BexJob));
+    const void* d = upload_jobs(jobs);
     cache_[key] = d;
     return (const BexJob*)d;
 }
@@ -357,7 +369,7 @@ const BexJob* Context::bfv_quant2_jobs(int level) {
         bex_fill_f64(job, moduli);
         jobs.push_back(job);
     }
-    const void* d = to_device(jobs.data(), jobs.size() * sizeof(BexJob));
+    const void* d = upload_jobs(jobs);
     cache_[key] = d;
     return (const BexJob*)d;
 }

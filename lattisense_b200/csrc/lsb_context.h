@@ -54,7 +54,8 @@ struct Context {
     const BexJob* moddown_jobs(int level);                  // 2 jobs (one per polynomial)
     const FinishMap* moddown_finish(int level, int addmask, int out_stride);  // rows (p,i); addmask bit p: add c_p
     const FinishMap* rescale_finish(int level, int npoly);
-    const FinishMap* finish_host(const FinishMap* dev);  // host copy of a map returned by the two builders above
+    const FinishMap* finish_host(const FinishMap* dev);
+    const BexMeta* bex_meta(const BexJob* dev);  // host description of a job array returned by the *_jobs builders  // host copy of a map returned by the two builders above
     const Tw* qlinv(int level);                             // [level]  q_level^-1 mod q_i
     const u32* permute_index(u64 gal);
     const BexJob* bfv_q_to_qmul_jobs(int level);            // 2 jobs: input ct -> extended ct
@@ -71,6 +72,8 @@ private:
     std::vector<void*> owned_;
     std::unordered_map<u64, const void*> cache_;
     std::unordered_map<const void*, FinishMap> fm_host_;
+    std::unordered_map<const void*, std::vector<BexMeta>> bex_meta_;
+    const void* upload_jobs(const std::vector<BexJob>& jobs);
     std::unique_ptr<Workspace> ws0_;
 };
 

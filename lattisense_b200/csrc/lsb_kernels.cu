@@ -193,14 +193,106 @@ __global__ void __launch_bounds__(kElemThreads) k_basis_extend(const __grid_cons
         job, g.mods, x, [&](int t) { return po[(size_t)job.other_slot[t] * N + j]; },
         [&](int t, u64 v) { pd[(size_t)job.dst_slot[t] * N + j] = v; });
 }
+// Fast path: plain CRT extension (ModUp / ModDown of the key-switch) with NS source limbs, every modulus below 2^47.
+// Two coefficients per thread (128-bit accesses), the job's constants staged in shared memory as doubles, the CRT on
+// the FP64 pipe (lsb_elem_core.h has the same arithmetic in its generic form; tests/emul checks it on the CPU).
+template <int NS>
+struct BexTargetC {
+    double qd, qinvd;
+    double vS[NS + 1];
+    TwD c[NS];
+    int slot, pad_;
+};
+template <int NS>
+__global__ void __launch_bounds__(kElemThreads) k_bex_f64(const __grid_constant__ BexArgs g) {
+    __shared__ BexTargetC<NS> sh[kBexMaxDst];
+    const BexJob& job = g.jobs[blockIdx.y];
+    const int nt = job.nt;
+    for (int t = threadIdx.x; t < nt; t += blockDim.x) {
+        const ModConst& m = g.mods[job.dst_mod[t]];
+        BexTargetC<NS>& c = sh[t];
+        c.qd = m.qd;
+        c.qinvd = m.qinvd;
+        c.slot = job.dst_slot[t];
+#pragma unroll
+        for (int i = 0; i < NS; i++) c.c[i] = job.qhat_mod_d[t][i];
+#pragma unroll
+        for (int v = 0; v <= NS; v++) c.vS[v] = f64_from_u64(job.vS[t][v]);
+    }
+    __syncthreads();
+    const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j2 >= g.N / 2) return;
+    const int b = blockIdx.z;
+    const u64* ps = g.src.at(b);
+    u64* pd = g.dst.at(b);
+    const size_t N = g.N;
+    double ya[NS], yb[NS];
+    double vfa = 0.0, vfb = 0.0;
+#pragma unroll
+    for (int i = 0; i < NS; i++) {
+        const W2 x = ld2(ps + (size_t)job.src_slot[i] * N, j2);
+        const ModConst& ms = g.mods[job.src_mod[i]];
+        const TwD qi = job.qhat_inv_d[i];
+        const double sf = job.s_f64[i];
+        ya[i] = f64_canon_d(f64_mulmod(f64_from_u64(x.a), qi, ms.qd), ms.qd, ms.qinvd);
+        yb[i] = f64_canon_d(f64_mulmod(f64_from_u64(x.b), qi, ms.qd), ms.qd, ms.qinvd);
+        vfa += ya[i] / sf;  // same float64 overflow estimate, same summation order as the generic path
+        vfb += yb[i] / sf;
+    }
+    const int va = (int)(u64)vfa, vb = (int)(u64)vfb;
+    for (int t = 0; t < nt; t++) {
+        const BexTargetC<NS>& c = sh[t];
+        double aa = 0.0, ab = 0.0;
+#pragma unroll
+        for (int i = 0; i < NS; i++) {
+            aa = d_add(aa, f64_mulmod(ya[i], c.c[i], c.qd));
+            ab = d_add(ab, f64_mulmod(yb[i], c.c[i], c.qd));
+        }
+        aa = d_add(aa, -c.vS[va]);
+        ab = d_add(ab, -c.vS[vb]);
+        W2 o;
+        o.a = f64_canon_u(aa, c.qd, c.qinvd);
+        o.b = f64_canon_u(ab, c.qd, c.qinvd);
+        st2(pd + (size_t)c.slot * N, j2, o);
+    }
+}
+
 void launch_basis_extend(const DeviceTables& dt, const BexJob* jobs, int njobs, BatchPtr src, BatchPtr dst,
-                         BatchPtr other, int batch, cudaStream_t s) {
+                         BatchPtr other, int batch, cudaStream_t s, const BexMeta* meta) {
     if (batch <= 0 || njobs <= 0) return;
-    BexArgs g{jobs, src, dst, other, dt.N, dt.mods};
-    dim3 grid((dt.N + kElemThreads - 1) / kElemThreads, njobs, batch);
-    ProfScope _ps(dt.prof, PK_BASIS_EXT, s, 0.0);
-    k_basis_extend<<<grid, kElemThreads, 0, s>>>(g);
-    LSB_CUDA(cudaGetLastError());
+    // consecutive jobs of the same class go in one launch
+    for (int j0 = 0; j0 < njobs;) {
+        const int fast_ns = (meta && meta[j0].f64_ok && !meta[j0].centered && meta[j0].mode == BEX_PLAIN && meta[j0].ns >= 2 &&
+                             meta[j0].ns <= 6)
+                                ? meta[j0].ns
+                                : 0;
+        int j1 = j0 + 1;
+        while (j1 < njobs) {
+            const int f = (meta && meta[j1].f64_ok && !meta[j1].centered && meta[j1].mode == BEX_PLAIN && meta[j1].ns >= 2 &&
+                           meta[j1].ns <= 6)
+                              ? meta[j1].ns
+                              : 0;
+            if (f != fast_ns) break;
+            j1++;
+        }
+        BexArgs g{jobs + j0, src, dst, other, dt.N, dt.mods};
+        ProfScope _ps(dt.prof, PK_BASIS_EXT, s, 0.0);
+        if (fast_ns) {
+            dim3 grid((dt.N / 2 + kElemThreads - 1) / kElemThreads, j1 - j0, batch);
+            switch (fast_ns) {
+                case 2: k_bex_f64<2><<<grid, kElemThreads, 0, s>>>(g); break;
+                case 3: k_bex_f64<3><<<grid, kElemThreads, 0, s>>>(g); break;
+                case 4: k_bex_f64<4><<<grid, kElemThreads, 0, s>>>(g); break;
+                case 5: k_bex_f64<5><<<grid, kElemThreads, 0, s>>>(g); break;
+                default: k_bex_f64<6><<<grid, kElemThreads, 0, s>>>(g); break;
+            }
+        } else {
+            dim3 grid((dt.N + kElemThreads - 1) / kElemThreads, j1 - j0, batch);
+            k_basis_extend<<<grid, kElemThreads, 0, s>>>(g);
+        }
+        LSB_CUDA(cudaGetLastError());
+        j0 = j1;
+    }
 }
 
 // ---- (a - b) * c (+ addend) ------------------------------------------------------------------------

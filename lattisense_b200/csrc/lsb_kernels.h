@@ -61,8 +61,12 @@ struct BexJob {
     TwD mulc_d[kBexMaxDst];
 };
 // jobs: device array of njobs BexJob; src/dst/other: per-batch-item blocks.
+// meta: host-side description of the jobs (selects the specialised kernels); nullptr: generic kernel
+struct BexMeta {
+    int ns, nt, mode, centered, f64_ok;
+};
 void launch_basis_extend(const DeviceTables& dt, const BexJob* jobs, int njobs, BatchPtr src, BatchPtr dst,
-                         BatchPtr other, int batch, cudaStream_t s);
+                         BatchPtr other, int batch, cudaStream_t s, const BexMeta* meta = nullptr);
 
 // ---- limb-wise kernels ----
 enum BinOp { OP_ADD = 0, OP_SUB = 1 };

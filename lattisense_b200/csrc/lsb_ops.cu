@@ -82,7 +82,10 @@ static void ks_core(OpEnv& e, int level, BatchPtr c_coeff, int coeff_slot0, Batc
     BatchPtr acc = bp_strided(scratch + (size_t)beta * lk * N, item_words);
     BatchPtr md = bp_strided(scratch + (size_t)(beta * lk + 2 * lk) * N, item_words);
 
-    launch_basis_extend(dt, c.modup_jobs(level, coeff_slot0), beta, c_coeff, ext, ext, nb, e.s);
+    {
+        const BexJob* jobs = c.modup_jobs(level, coeff_slot0);
+        launch_basis_extend(dt, jobs, beta, c_coeff, ext, ext, nb, e.s, c.bex_meta(jobs));
+    }
     {
         RowMap m;
         m.n = 0;
@@ -131,7 +134,10 @@ static void ks_core(OpEnv& e, int level, BatchPtr c_coeff, int coeff_slot0, Batc
             }
         launch_ntt(dt, acc, acc, m, nb, true, e.s);
     }
-    launch_basis_extend(dt, c.moddown_jobs(level), 2, acc, md, md, nb, e.s);
+    {
+        const BexJob* jobs = c.moddown_jobs(level);
+        launch_basis_extend(dt, jobs, 2, acc, md, md, nb, e.s, c.bex_meta(jobs));
+    }
     {
         const FinishMap* fm = c.moddown_finish(level, addmask, res_ps);
         NttFinish fin{fm, c.finish_host(fm), acc, addend, res, addmask != 0};

@@ -99,7 +99,12 @@ CKKS_BTP_N15 = Params("ckks_btp_n32768", SCHEME_CKKS, 15, _BTP_Q, _BTP_P, scale=
 # small-ring variants (not NTT-friendly for every reference prime, so use the n=8192 sets' primes: = 1 mod 2^14)
 CKKS_N12 = Params("ckks_small_n4096", SCHEME_CKKS, 12, CKKS_N13.q[:4], CKKS_N13.p, scale=2.0 ** 30)
 
-ALL_PARAMS = {p.name: p for p in (BFV_N14, BFV_N13, CKKS_N14, CKKS_N13, CKKS_BTP_N16, CKKS_BTP_N13, CKKS_BTP_N15, CKKS_N12)}
+# parity-only set with 3-limb key-switch digits (alpha = 3; digits of 3, 2 and 1 limbs depending on the level):
+# exercises the generic-beta / generic-alpha code paths with primes below 2^47 (moduli borrowed from CKKS_N14)
+CKKS_WIDE_N13 = Params("ckks_wide_digit_n8192", SCHEME_CKKS, 13, CKKS_N14.q[:7], CKKS_N14.q[7:10], scale=2.0 ** 34)
+
+ALL_PARAMS = {p.name: p for p in (BFV_N14, BFV_N13, CKKS_N14, CKKS_N13, CKKS_BTP_N16, CKKS_BTP_N13, CKKS_BTP_N15, CKKS_N12,
+                                     CKKS_WIDE_N13)}
 
 
 # ---------------------------------------------------------------------------------------------

@@ -47,7 +47,7 @@ def rand_evk(o, rng, key_level):
     return out
 
 
-SETS = [R.CKKS_N12, R.CKKS_N13, R.CKKS_N14, R.BFV_N13, R.BFV_N14]
+SETS = [R.CKKS_N12, R.CKKS_N13, R.CKKS_N14, R.BFV_N13, R.BFV_N14, R.CKKS_WIDE_N13]
 IDS = [p.name for p in SETS]
 
 
@@ -76,7 +76,7 @@ def test_mult_relin_rescale_parity(params):
     rng = np.random.default_rng(31)
     L = params.max_level
     rlk = o.gen_rlk(s, 77, L)
-    for level in sorted({L, max(1, L // 2), 1}):
+    for level in sorted({L, max(1, L // 2), 1} | ({4, 5} if L >= 5 else set())):
         a, b = rand_ct(o, rng, level), rand_ct(o, rng, level)
         want3 = o.mult(a, b)
         got3 = g.mult(a, b)

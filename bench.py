@@ -405,8 +405,15 @@ def run_ours(args):
                            "path": "C ABI lsb_upload + lsb_mult_relin_rescale + lsb_download (include/lsb200.h), pinned host buffers"},
         "gpu_launches": launches,
         "clocks": clocks,
-        "roofline": {"bound": "hbm", "kernel": "k_ntt_single<14> (fwd+inv, in-step average)",
-                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        "roofline": {"bound": "hbm", "kernel": "k_ntt_cluster<14,*,ArithF64> (forward incl. its fused finish epilogue + inverse, in-step average)",
+                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     # DRAM bytes per launch: ncu --set full measured 0.974 x the algorithmic 16*N bytes per limb transform
+                     # (profiles/r01_ntt14_cluster_ncu.txt: 1.075 GB read + 1.018 GB written for 8192 limbs of N=2^14)
+                     "traffic": 0.974 * ntt_bytes / max(ntt_k, 1),
+                     "algorithmic_bytes_per_launch": ntt_bytes / max(ntt_k, 1),
+                     # second roof: the FP64 pipe, 1.015 M DFMA-class ops per limb transform at the measured
+                     # 57.8 lanes/clk/SM = 4.36 TB/s of algorithmic NTT traffic if the pipe never idled
+                     "fp64_pipe_roof_gbs": 4360.0, "frac_of_fp64_roof": achieved / 4360.0,
                      "peak_source": peak_src, "launches": ntt_k, "ms_per_launch": ntt_ms / max(ntt_k, 1),
                      "share_of_step": ntt_ms / tot_ms if tot_ms else None,
                      "standalone_ntt_gbs": ntt_alone, "standalone_frac": ntt_alone / peak},

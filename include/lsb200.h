@@ -102,6 +102,30 @@ long long lsb_launch_count(lsb_context_t ctx);
 void lsb_profile_enable(lsb_context_t ctx, int on);
 int lsb_profile_read(lsb_context_t ctx, int kind, double* ms, long long* kernels, double* algorithmic_bytes);
 
+/* ---- multi-GPU: limb-sharded hybrid key-switch (no reference counterpart -- the reference GPU
+ * path is single-device, mega_ag_runners/gpu/gpu_wrapper.cu:141-391) ----
+ * World of `world` ranks, one context per GPU.  Rank r owns Q limbs {i : i % world == r} and P limbs
+ * {j : j % world == r} of every polynomial and of the evaluation key.  Buffers of one rank (u64 words, N = 2^log_n):
+ *   c_own_ntt  [nq_own][N]          owned Q limbs of the polynomial to switch, NTT domain
+ *   coeff_own  [cq][N]              phase-1 output (cq = ceil((level+1)/world); rows >= nq_own unused)
+ *   coeff_all  [world][cq][N]       all-gather of coeff_own over the ranks (caller: NCCL)
+ *   evk_own    [beta][2][nq_own+np_own][N]   owned limbs of the key (Q limbs first, then P limbs)
+ *   acc_own    [2][nq_own+np_own][N]
+ *   accP_own   [2][cp][N]           owned P limbs of the accumulators, coefficient domain (cp = ceil(k/world))
+ *   accP_all   [world][2][cp][N]    all-gather of accP_own
+ *   addend_own / out_own [2][nq_own][N]      out = ModDown(acc) (+ addend), owned Q limbs, NTT domain
+ * Every limb produced equals the same limb of the single-GPU lsb_relin / lsb_rotate key-switch bit for bit. */
+int lsb_ks_shard_layout(lsb_context_t ctx, int level, int world, int rank, int* nq_own, int* np_own, int* cq, int* cp,
+                        int* own_q, int* own_p);
+int lsb_ks_shard_begin(lsb_context_t ctx, int level, int world, int rank, const uint64_t* d_c_own_ntt,
+                       uint64_t* d_coeff_own, int batch, void* stream);
+int lsb_ks_shard_inner(lsb_context_t ctx, int level, int world, int rank, const uint64_t* d_coeff_all,
+                       const uint64_t* d_c_own_ntt, const uint64_t* d_evk_own, uint64_t* d_acc_own, uint64_t* d_accP_own,
+                       int batch, void* stream);
+int lsb_ks_shard_end(lsb_context_t ctx, int level, int world, int rank, const uint64_t* d_accP_all,
+                     const uint64_t* d_acc_own, const uint64_t* d_addend_own /* may be NULL */, uint64_t* d_out_own,
+                     int batch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

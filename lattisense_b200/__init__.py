@@ -69,6 +69,10 @@ def lib():
     L.lsb_mul_plain_ringt.argtypes = [vp, ci, ci, vp, vp, vp, ci, vp]
     L.lsb_mult_relin.argtypes = [vp, ci, vp, vp, vp, ci, vp, ci, vp]
     L.lsb_mult_relin_rescale.argtypes = [vp, ci, vp, vp, vp, ci, vp, ci, vp]
+    L.lsb_ks_shard_layout.argtypes = [vp, ci, ci, ci, i32p, i32p, i32p, i32p, i32p, i32p]
+    L.lsb_ks_shard_begin.argtypes = [vp, ci, ci, ci, vp, vp, ci, vp]
+    L.lsb_ks_shard_inner.argtypes = [vp, ci, ci, ci, vp, vp, vp, vp, vp, ci, vp]
+    L.lsb_ks_shard_end.argtypes = [vp, ci, ci, ci, vp, vp, vp, vp, ci, vp]
     L.lsb_launch_count.restype = C.c_longlong
     L.lsb_launch_count.argtypes = [vp]
     L.lsb_profile_enable.argtypes = [vp, ci]

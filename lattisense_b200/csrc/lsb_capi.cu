@@ -239,4 +239,50 @@ int lsb_profile_read(lsb_context_t h, int kind, double* ms, long long* kernels, 
     LSB_API_END(1)
 }
 
+
+// ---- limb-sharded key-switch (include/lsb200.h, "multi-GPU" section) ----
+int lsb_ks_shard_layout(lsb_context_t h, int level, int world, int rank, int* nq_own, int* np_own, int* cq, int* cp,
+                        int* own_q, int* own_p) {
+    LSB_API_BEGIN
+    LSB_CHECK(h && h->c, "lsb: null context");
+    const ShardPlan& sp = h->c->shard_plan(level, world, rank);
+    if (nq_own) *nq_own = sp.nq_own;
+    if (np_own) *np_own = sp.np_own;
+    if (cq) *cq = sp.cq;
+    if (cp) *cp = sp.cp;
+    if (own_q)
+        for (int u = 0; u < sp.nq_own; u++) own_q[u] = sp.own_q[u];
+    if (own_p)
+        for (int u = 0; u < sp.np_own; u++) own_p[u] = sp.own_p[u];
+    return 0;
+    LSB_API_END(1)
+}
+int lsb_ks_shard_begin(lsb_context_t h, int level, int world, int rank, const uint64_t* d_c_own_ntt, uint64_t* d_coeff_own,
+                       int batch, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        const ShardPlan& sp = e.c.shard_plan(level, world, rank);
+        op_ks_shard_begin(e, sp, dense(d_c_own_ntt, (size_t)sp.nq_own * e.c.N), dense(d_coeff_own, (size_t)sp.cq * e.c.N), batch);
+    });
+}
+int lsb_ks_shard_inner(lsb_context_t h, int level, int world, int rank, const uint64_t* d_coeff_all,
+                       const uint64_t* d_c_own_ntt, const uint64_t* d_evk_own, uint64_t* d_acc_own, uint64_t* d_accP_own,
+                       int batch, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        const ShardPlan& sp = e.c.shard_plan(level, world, rank);
+        const size_t N = e.c.N;
+        op_ks_shard_inner(e, sp, dense(d_coeff_all, (size_t)world * sp.cq * N), dense(d_c_own_ntt, (size_t)sp.nq_own * N),
+                          d_evk_own, dense(d_acc_own, (size_t)2 * sp.n_own * N), dense(d_accP_own, (size_t)2 * sp.cp * N), batch);
+    });
+}
+int lsb_ks_shard_end(lsb_context_t h, int level, int world, int rank, const uint64_t* d_accP_all, const uint64_t* d_acc_own,
+                     const uint64_t* d_addend_own, uint64_t* d_out_own, int batch, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        const ShardPlan& sp = e.c.shard_plan(level, world, rank);
+        const size_t N = e.c.N;
+        const size_t w = (size_t)2 * sp.nq_own * N;
+        op_ks_shard_end(e, sp, dense(d_accP_all, (size_t)world * 2 * sp.cp * N), dense(d_acc_own, (size_t)2 * sp.n_own * N),
+                        dense(d_addend_own ? d_addend_own : d_out_own, w), d_addend_own != nullptr, dense(d_out_own, w), batch);
+    });
+}
+
 }  // extern "C"

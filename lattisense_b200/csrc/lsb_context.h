@@ -4,7 +4,9 @@
 #pragma once
 #include <mutex>
 #include <unordered_map>
+#include <memory>
 #include "lsb_kernels.h"
+#include "lsb_shard.h"
 
 namespace lsb {
 
@@ -64,6 +66,12 @@ struct Context {
     const ScaleUpConsts* bfv_scale_up_consts(int level);
 
     Workspace& default_workspace() { return *ws0_; }
+    // limb-sharded key-switch tables (lsb_shard.cu), cached per (level, world, rank)
+    const ShardPlan& shard_plan(int level, int world, int rank);
+    const void* upload_raw(const void* host, size_t bytes) {
+        std::lock_guard<std::mutex> lk(mu_);
+        return to_device(host, bytes);
+    }
 
 private:
     void* to_device(const void* host, size_t bytes);
@@ -72,6 +80,8 @@ private:
     std::vector<void*> owned_;
     std::unordered_map<u64, const void*> cache_;
     std::unordered_map<const void*, FinishMap> fm_host_;
+    std::mutex shard_mu_;
+    std::unordered_map<u64, std::unique_ptr<ShardPlan>> shard_plans_;
     std::unordered_map<const void*, std::vector<BexMeta>> bex_meta_;
     const void* upload_jobs(const std::vector<BexJob>& jobs);
     std::unique_ptr<Workspace> ws0_;

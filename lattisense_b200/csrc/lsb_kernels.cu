@@ -341,9 +341,10 @@ __global__ void __launch_bounds__(kElemThreads) k_ks_inner(const __grid_constant
     const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
     if (j2 >= g.N / 2) return;
     const KsInnerArgs& a = g.a;
-    const int t = blockIdx.y, b = blockIdx.z;
-    const int lk = a.l + a.k, klimbs = a.key_level + 1 + a.k;
-    const int key_limb = t < a.l ? t : a.key_level + 1 + (t - a.l);
+    const int row = blockIdx.y, b = blockIdx.z;
+    const int t = a.mapped ? a.tmap[row] : row;
+    const int lk = a.mapped ? a.rows : a.l + a.k, klimbs = a.mapped ? a.rows : a.key_level + 1 + a.k;
+    const int key_limb = a.mapped ? row : (t < a.l ? t : a.key_level + 1 + (t - a.l));
     const ModConst& mc = g.mods[t < a.l ? t : a.nq + (t - a.l)];
     const size_t N = g.N;
     const u64* pext = a.ext.at(b);
@@ -355,7 +356,7 @@ __global__ void __launch_bounds__(kElemThreads) k_ks_inner(const __grid_constant
         double s0a = 0.0, s0b = 0.0, s1a = 0.0, s1b = 0.0;
         for (int d = 0; d < a.beta; d++) {
             const bool own = t < a.l && t >= d * a.alpha && t < (d + 1) * a.alpha;
-            const W2 x = own ? ld2(pc + (size_t)t * N, j2) : ld2(pext + (size_t)(d * lk + t) * N, j2);
+            const W2 x = own ? ld2(pc + (size_t)row * N, j2) : ld2(pext + (size_t)(d * lk + row) * N, j2);
             const W2 e0 = ld2(a.evk + ((size_t)(d * 2 + 0) * klimbs + key_limb) * N, j2);
             const W2 e1 = ld2(a.evk + ((size_t)(d * 2 + 1) * klimbs + key_limb) * N, j2);
             const double xa = f64_from_u64(x.a), xb = f64_from_u64(x.b);
@@ -369,8 +370,8 @@ __global__ void __launch_bounds__(kElemThreads) k_ks_inner(const __grid_constant
         o0.b = f64_canon_u(s0b, q, qinv);
         o1.a = f64_canon_u(s1a, q, qinv);
         o1.b = f64_canon_u(s1b, q, qinv);
-        st2(pacc + (size_t)t * N, j2, o0);
-        st2(pacc + (size_t)(lk + t) * N, j2, o1);
+        st2(pacc + (size_t)row * N, j2, o0);
+        st2(pacc + (size_t)(lk + row) * N, j2, o1);
         return;
     }
     const BarrettQ bq = mc.bq;
@@ -378,7 +379,7 @@ __global__ void __launch_bounds__(kElemThreads) k_ks_inner(const __grid_constant
     int terms = 0;
     for (int d = 0; d < a.beta; d++) {
         const bool own = t < a.l && t >= d * a.alpha && t < (d + 1) * a.alpha;
-        const W2 x = own ? ld2(pc + (size_t)t * N, j2) : ld2(pext + (size_t)(d * lk + t) * N, j2);
+        const W2 x = own ? ld2(pc + (size_t)row * N, j2) : ld2(pext + (size_t)(d * lk + row) * N, j2);
         const W2 e0 = ld2(a.evk + ((size_t)(d * 2 + 0) * klimbs + key_limb) * N, j2);
         const W2 e1 = ld2(a.evk + ((size_t)(d * 2 + 1) * klimbs + key_limb) * N, j2);
         acc_mad(s0a, x.a, e0.a);
@@ -399,15 +400,17 @@ __global__ void __launch_bounds__(kElemThreads) k_ks_inner(const __grid_constant
     o0.b = reduce_wide(s0b.lo, s0b.hi, bq);
     o1.a = reduce_wide(s1a.lo, s1a.hi, bq);
     o1.b = reduce_wide(s1b.lo, s1b.hi, bq);
-    st2(pacc + (size_t)t * N, j2, o0);
-    st2(pacc + (size_t)(lk + t) * N, j2, o1);
+    st2(pacc + (size_t)row * N, j2, o0);
+    st2(pacc + (size_t)(lk + row) * N, j2, o1);
 }
 void launch_ks_inner(const DeviceTables& dt, const KsInnerArgs& a, int batch, cudaStream_t s) {
     if (batch <= 0) return;
     KsInnerK g{a, dt.N, dt.mods};
     ProfScope _ps(dt.prof, PK_KS_INNER, s, 8.0 * dt.N * (a.l + a.k) * (batch * (a.beta + 2.0) + 2.0 * a.beta));
-    if (a.f64 && a.beta <= 16) k_ks_inner<true><<<elem_grid(dt.N, a.l + a.k, batch), kElemThreads, 0, s>>>(g);
-    else k_ks_inner<false><<<elem_grid(dt.N, a.l + a.k, batch), kElemThreads, 0, s>>>(g);
+    const int rows = a.mapped ? a.rows : a.l + a.k;
+    if (rows <= 0) return;
+    if (a.f64 && a.beta <= 16) k_ks_inner<true><<<elem_grid(dt.N, rows, batch), kElemThreads, 0, s>>>(g);
+    else k_ks_inner<false><<<elem_grid(dt.N, rows, batch), kElemThreads, 0, s>>>(g);
     LSB_CUDA(cudaGetLastError());
 }
 

@@ -108,6 +108,10 @@ struct KsInnerArgs {
     int l, k, beta, alpha, key_level;
     int nq;  // modulus index of P_0
     int f64;   // every prime involved is below 2^47 (FP64-pipe variant)
+    // limb-sharded variant (lsb_shard.cu): only `rows` of the l+k limbs are present, compacted; row r is global limb
+    // tmap[r] (Q index, or l + P index); ext / acc / evk / cntt are all indexed by the compact row
+    int mapped, rows;
+    uint8_t tmap[64];
     int fold;  // products that may be accumulated before a reduction: fold * max(q) < 2^63 (reduce_wide bound)
 };
 void launch_ks_inner(const DeviceTables& dt, const KsInnerArgs& a, int batch, cudaStream_t s);

@@ -111,6 +111,8 @@ static void ks_core(OpEnv& e, int level, BatchPtr c_coeff, int coeff_slot0, Batc
     ia.alpha = alpha;
     ia.key_level = key_level;
     ia.nq = c.nq;
+    ia.mapped = 0;
+    ia.rows = 0;
     {
         u64 qmax = 0;
         for (int i = 0; i < l; i++) qmax = std::max(qmax, c.moduli[i]);

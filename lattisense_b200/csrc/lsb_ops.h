@@ -50,6 +50,14 @@ void op_mult_relin(OpEnv& e, int level, BatchPtr a, BatchPtr b, const u64* rlk, 
 void op_mult_relin_rescale(OpEnv& e, int level, BatchPtr a, BatchPtr b, const u64* rlk, int key_level, BatchPtr out2,
                            int batch);
 
+// limb-sharded key-switch phases (lsb_shard.cu; the all-gathers between them are the caller's)
+struct ShardPlan;
+void op_ks_shard_begin(OpEnv& e, const ShardPlan& sp, BatchPtr c_own_ntt, BatchPtr coeff_own, int batch);
+void op_ks_shard_inner(OpEnv& e, const ShardPlan& sp, BatchPtr coeff_all, BatchPtr c_own_ntt, const u64* evk_own,
+                       BatchPtr acc_own, BatchPtr accP_own, int batch);
+void op_ks_shard_end(OpEnv& e, const ShardPlan& sp, BatchPtr accP_all, BatchPtr acc_own, BatchPtr addend_own, bool has_addend,
+                     BatchPtr out_own, int batch);
+
 // plain batched NTT over [rows][N] limbs whose moduli are mod_idx[r % period]
 void op_ntt(OpEnv& e, BatchPtr in, BatchPtr out, int rows, const int* mod_idx, int period, bool inverse, int batch);
 

@@ -61,3 +61,106 @@ class Ranks:
     def close(self):
         if self.world > 1 and dist.is_initialized():
             dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------------------------------------
+# Limb-sharded key-switch (third mode): the one place where the path has a real exchange step
+# ---------------------------------------------------------------------------------------------
+def shard_layout(level, k, world, rank):
+    """Pure host logic (no GPU): which Q / P limbs rank `rank` owns and the padded counts of the gathered buffers.
+    Must agree with lsb::ShardPlan (csrc/lsb_shard.cu) -- checked against lsb_ks_shard_layout in the GPU tests."""
+    l = level + 1
+    own_q = list(range(rank, l, world))
+    own_p = list(range(rank, k, world))
+    return {"own_q": own_q, "own_p": own_p, "cq": -(-l // world), "cp": -(-k // world)}
+
+
+def shard_poly(arr, own_q):
+    """[..., l, N] -> [..., nq_own, N]: the owned Q limbs of a polynomial / ciphertext"""
+    return arr[..., own_q, :].copy()
+
+
+def shard_evk(evk, key_level, k, own_q, own_p):
+    """[beta][2][key_level+1+k][N] -> [beta][2][nq_own+np_own][N] (owned Q limbs first, then owned P limbs)"""
+    idx = list(own_q) + [key_level + 1 + j for j in own_p]
+    return evk[:, :, idx, :].copy()
+
+
+def unshard_ct(parts, level, world):
+    """inverse of shard_poly over all ranks: list of [2][nq_own_r][N] -> [2][l][N]"""
+    import numpy as np
+    l = level + 1
+    out = np.zeros((2, l, parts[0].shape[-1]), dtype=parts[0].dtype)
+    for r, part in enumerate(parts):
+        for u, i in enumerate(range(r, l, world)):
+            out[:, i, :] = part[:, u, :]
+    return out
+
+
+class ShardedKeySwitch:
+    """One rank of the limb-sharded hybrid key-switch: three local phases (C ABI lsb_ks_shard_*) around two
+    all-gathers.  `gather(local, out)` fills `out` ([world, *local.shape]) with every rank's `local`; the default is
+    torch.distributed.all_gather_into_tensor (NCCL over NVLink on the GPU box), tests pass an emulation."""
+
+    def __init__(self, ctx, level, world, rank, device=None, gather=None):
+        import ctypes as C
+        import lattisense_b200 as L
+        self.L, self.C, self.ctx = L, C, ctx
+        self.level, self.world, self.rank = level, world, rank
+        lay = shard_layout(level, ctx.k, world, rank)
+        self.own_q, self.own_p, self.cq, self.cp = lay["own_q"], lay["own_p"], lay["cq"], lay["cp"]
+        vals = [C.c_int() for _ in range(4)]
+        oq = (C.c_int * max(1, len(self.own_q)))()
+        op = (C.c_int * max(1, len(self.own_p)))()
+        L._check(L.lib().lsb_ks_shard_layout(ctx.h, level, world, rank, *[C.byref(v) for v in vals], oq, op))
+        got = ([v.value for v in vals], list(oq)[:len(self.own_q)], list(op)[:len(self.own_p)])
+        want = ([len(self.own_q), len(self.own_p), self.cq, self.cp], self.own_q, self.own_p)
+        if got != want:
+            raise L.LsbError("shard layout mismatch between host and library: %r vs %r" % (got, want))
+        self.nq_own, self.np_own = len(self.own_q), len(self.own_p)
+        self.n_own = self.nq_own + self.np_own
+        self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.gather = gather or self._nccl_gather
+        N = ctx.N
+        z = lambda *shape: torch.zeros(shape, dtype=torch.int64, device=self.device)
+        self.coeff_own = z(self.cq, N)
+        self.coeff_all = z(world, self.cq, N)
+        self.acc_own = z(2, max(self.n_own, 1), N)
+        self.accP_own = z(2, self.cp, N)
+        self.accP_all = z(world, 2, self.cp, N)
+
+    @staticmethod
+    def _nccl_gather(local, out):
+        # concatenation form ([world * rows, ...]): accepted by NCCL and gloo alike
+        dist.all_gather_into_tensor(out.view(-1, *local.shape[1:]), local)
+
+    def _stream(self):
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def begin(self, c_own_ntt):
+        L = self.L
+        L._check(L.lib().lsb_ks_shard_begin(self.ctx.h, self.level, self.world, self.rank, c_own_ntt.data_ptr(),
+                                            self.coeff_own.data_ptr(), 1, self._stream()))
+
+    def inner(self, c_own_ntt, evk_own):
+        L = self.L
+        L._check(L.lib().lsb_ks_shard_inner(self.ctx.h, self.level, self.world, self.rank, self.coeff_all.data_ptr(),
+                                            c_own_ntt.data_ptr(), evk_own.data_ptr(), self.acc_own.data_ptr(),
+                                            self.accP_own.data_ptr(), 1, self._stream()))
+
+    def end(self, addend_own, out_own):
+        L = self.L
+        L._check(L.lib().lsb_ks_shard_end(self.ctx.h, self.level, self.world, self.rank, self.accP_all.data_ptr(),
+                                          self.acc_own.data_ptr(), addend_own.data_ptr() if addend_own is not None else None,
+                                          out_own.data_ptr(), 1, self._stream()))
+
+    def run(self, c_own_ntt, evk_own, addend_own=None):
+        """c_own_ntt [nq_own][N], evk_own [beta][2][n_own][N], addend_own [2][nq_own][N] (int64 views of u64 residues,
+        on this rank's GPU) -> out_own [2][nq_own][N]"""
+        out = torch.empty((2, max(self.nq_own, 1), self.ctx.N), dtype=torch.int64, device=self.device)
+        self.begin(c_own_ntt)
+        self.gather(self.coeff_own, self.coeff_all)
+        self.inner(c_own_ntt, evk_own)
+        self.gather(self.accP_own, self.accP_all)
+        self.end(addend_own, out)
+        return out[:, :self.nq_own]

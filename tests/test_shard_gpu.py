@@ -1,0 +1,90 @@
+"""Limb-sharded key-switch (third mode) on ONE GPU: the G ranks are emulated as G sequential calls of
+each phase on the same device (the kernels never wait on one another), the two all-gathers as tensor copies.  Every
+limb each rank produces must equal the same limb of the oracle's single-device relinearisation."""
+import numpy as np
+import pytest
+import torch
+
+import fhe_ref as R
+import lattisense_b200 as L
+from lattisense_b200.dist import ShardedKeySwitch, shard_evk, shard_poly, unshard_ct
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand_ct(o, rng, level, npoly):
+    out = np.zeros((npoly, level + 1, o.N), dtype=np.uint64)
+    for i in range(level + 1):
+        out[:, i, :] = rng.integers(0, o.p.q[i], size=(npoly, o.N), dtype=np.uint64)
+    return out
+
+
+def _rand_evk(o, rng, key_level):
+    shape = o.evk_shape(key_level)
+    out = np.zeros(shape, dtype=np.uint64)
+    for i, m in enumerate(o.p.q[:key_level + 1] + o.p.p):
+        out[:, :, i, :] = rng.integers(0, m, size=(shape[0], 2, o.N), dtype=np.uint64)
+    return out
+
+
+def _dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a).view(np.int64)).cuda()
+
+
+def _run_emulated(ctx, params, level, world, ct3, evk, with_addend):
+    ranks = [ShardedKeySwitch(ctx, level, world, r, gather=lambda a, b: None) for r in range(world)]
+    c_own = [_dev(shard_poly(ct3[2], sk.own_q)) if sk.nq_own else torch.zeros((1, ctx.N), dtype=torch.int64).cuda()
+             for sk in ranks]
+    evk_own = [_dev(shard_evk(evk, level, params.k, sk.own_q, sk.own_p)) if sk.n_own else None for sk in ranks]
+    add_own = [_dev(shard_poly(ct3[:2], sk.own_q)) if (with_addend and sk.nq_own) else None for sk in ranks]
+    for sk, c in zip(ranks, c_own):
+        sk.begin(c)
+    coeff_all = torch.stack([sk.coeff_own for sk in ranks])
+    for sk, c, e in zip(ranks, c_own, evk_own):
+        sk.coeff_all.copy_(coeff_all)
+        if sk.n_own:
+            sk.inner(c, e)
+    accp_all = torch.stack([sk.accP_own for sk in ranks])
+    parts = []
+    for sk, a in zip(ranks, add_own):
+        sk.accP_all.copy_(accp_all)
+        out = torch.zeros((2, max(sk.nq_own, 1), ctx.N), dtype=torch.int64).cuda()
+        if sk.nq_own:
+            sk.end(a, out)
+        torch.cuda.synchronize()
+        parts.append(out[:, :sk.nq_own].cpu().numpy().view(np.uint64))
+    return unshard_ct(parts, level, world)
+
+
+CASES = [(R.CKKS_N13, None, 2), (R.CKKS_N13, 2, 3), (R.CKKS_WIDE_N13, None, 2), (R.CKKS_WIDE_N13, 4, 4),
+         (R.CKKS_N14, 3, 2), (R.CKKS_N14, None, 8), (R.CKKS_BTP_N13, 24, 8), (R.CKKS_BTP_N13, 9, 4)]
+
+
+@pytest.mark.parametrize("params,level,world", CASES, ids=["%s-L%s-G%d" % (p.name, lv, w) for p, lv, w in CASES])
+def test_sharded_relin_matches_oracle(params, level, world):
+    o = R.Oracle(params)
+    ctx = L.Context(params.scheme, params.logN, params.q, params.p, params.t)
+    level = params.max_level if level is None else level
+    rng = np.random.default_rng(100 + world)
+    ct3 = _rand_ct(o, rng, level, 3)
+    evk = _rand_evk(o, rng, level)
+    want = o.relin(ct3, evk)
+    got = _run_emulated(ctx, params, level, world, ct3, evk, True)
+    assert np.array_equal(got, want)
+    # without the (c0, c1) addend: the bare key-switch of c2 (what a rotation adds c0 to)
+    ct3z = ct3.copy()
+    ct3z[:2] = 0
+    assert np.array_equal(_run_emulated(ctx, params, level, world, ct3z, evk, False), o.relin(ct3z, evk))
+    ctx.close()
+
+
+def test_n65536_sharded_over_8_ranks():
+    params = R.CKKS_BTP_N16
+    o = R.Oracle(params)
+    ctx = L.Context(params.scheme, params.logN, params.q, params.p, params.t)
+    level = 24
+    rng = np.random.default_rng(7)
+    ct3 = _rand_ct(o, rng, level, 3)
+    evk = _rand_evk(o, rng, level)
+    assert np.array_equal(_run_emulated(ctx, params, level, 8, ct3, evk, True), o.relin(ct3, evk))
+    ctx.close()

@@ -122,6 +122,16 @@ int lsb_ks_shard_begin(lsb_context_t ctx, int level, int world, int rank, const 
 int lsb_ks_shard_inner(lsb_context_t ctx, int level, int world, int rank, const uint64_t* d_coeff_all,
                        const uint64_t* d_c_own_ntt, const uint64_t* d_evk_own, uint64_t* d_acc_own, uint64_t* d_accP_own,
                        int batch, void* stream);
+/* Fused compute + collective: the same phases with the all-gather done INSIDE the INTT kernel that produces the
+ * limbs.  peer_*[r] is rank r's gathered buffer (coeff_all / accP_all) as mapped into THIS process (this rank's own
+ * buffer at index `rank`; e.g. torch.distributed._symmetric_memory buffer_ptrs).  The kernel stores each output
+ * word into all `world` buffers over NVLink peer memory; the caller only places a cross-rank barrier (no NCCL
+ * collective) before the next phase reads the gathered buffer, and one before the buffers are overwritten again. */
+int lsb_ks_shard_begin_p2p(lsb_context_t ctx, int level, int world, int rank, const uint64_t* d_c_own_ntt,
+                           uint64_t* const* peer_coeff_all, void* stream);
+int lsb_ks_shard_inner_p2p(lsb_context_t ctx, int level, int world, int rank, const uint64_t* d_coeff_all,
+                           const uint64_t* d_c_own_ntt, const uint64_t* d_evk_own, uint64_t* d_acc_own,
+                           uint64_t* const* peer_accP_all, void* stream);
 int lsb_ks_shard_end(lsb_context_t ctx, int level, int world, int rank, const uint64_t* d_accP_all,
                      const uint64_t* d_acc_own, const uint64_t* d_addend_own /* may be NULL */, uint64_t* d_out_own,
                      int batch, void* stream);

@@ -72,6 +72,8 @@ def lib():
     L.lsb_ks_shard_layout.argtypes = [vp, ci, ci, ci, i32p, i32p, i32p, i32p, i32p, i32p]
     L.lsb_ks_shard_begin.argtypes = [vp, ci, ci, ci, vp, vp, ci, vp]
     L.lsb_ks_shard_inner.argtypes = [vp, ci, ci, ci, vp, vp, vp, vp, vp, ci, vp]
+    L.lsb_ks_shard_begin_p2p.argtypes = [vp, ci, ci, ci, vp, vp, vp]
+    L.lsb_ks_shard_inner_p2p.argtypes = [vp, ci, ci, ci, vp, vp, vp, vp, vp, vp]
     L.lsb_ks_shard_end.argtypes = [vp, ci, ci, ci, vp, vp, vp, vp, ci, vp]
     L.lsb_launch_count.restype = C.c_longlong
     L.lsb_launch_count.argtypes = [vp]

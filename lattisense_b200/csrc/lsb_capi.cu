@@ -274,6 +274,25 @@ int lsb_ks_shard_inner(lsb_context_t h, int level, int world, int rank, const ui
                           d_evk_own, dense(d_acc_own, (size_t)2 * sp.n_own * N), dense(d_accP_own, (size_t)2 * sp.cp * N), batch);
     });
 }
+int lsb_ks_shard_begin_p2p(lsb_context_t h, int level, int world, int rank, const uint64_t* d_c_own_ntt,
+                           uint64_t* const* peer_coeff_all, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        const ShardPlan& sp = e.c.shard_plan(level, world, rank);
+        LSB_CHECK(peer_coeff_all, "lsb: null peer table");
+        op_ks_shard_begin(e, sp, dense(d_c_own_ntt, (size_t)sp.nq_own * e.c.N), dense(d_c_own_ntt, 0), 1, peer_coeff_all);
+    });
+}
+int lsb_ks_shard_inner_p2p(lsb_context_t h, int level, int world, int rank, const uint64_t* d_coeff_all,
+                           const uint64_t* d_c_own_ntt, const uint64_t* d_evk_own, uint64_t* d_acc_own,
+                           uint64_t* const* peer_accP_all, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        const ShardPlan& sp = e.c.shard_plan(level, world, rank);
+        const size_t N = e.c.N;
+        LSB_CHECK(peer_accP_all, "lsb: null peer table");
+        op_ks_shard_inner(e, sp, dense(d_coeff_all, (size_t)world * sp.cq * N), dense(d_c_own_ntt, (size_t)sp.nq_own * N),
+                          d_evk_own, dense(d_acc_own, (size_t)2 * sp.n_own * N), dense(d_acc_own, 0), 1, peer_accP_all);
+    });
+}
 int lsb_ks_shard_end(lsb_context_t h, int level, int world, int rank, const uint64_t* d_accP_all, const uint64_t* d_acc_own,
                      const uint64_t* d_addend_own, uint64_t* d_out_own, int batch, void* stream) {
     return run_op(h, stream, [&](OpEnv& e) {

@@ -32,7 +32,11 @@ void launch_ntt(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap&
 // cluster kernel (lsb_ntt_cluster.cu); launch_ntt dispatches to it unless LSB_NTT_IMPL=single
 struct NttFinish;
 void launch_ntt_cluster(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap& map, int batch, bool inverse,
-                        const std::vector<uint8_t>& f64_ok, bool allow_f64, cudaStream_t s, const NttFinish* fin = nullptr);
+                        const std::vector<uint8_t>& f64_ok, bool allow_f64, cudaStream_t s, const NttFinish* fin = nullptr,
+                        u64* const* peers = nullptr, int npeer = 0);
+// inverse NTT whose outputs go to word offset map.out_slot[r] * N of each of the `npeer` buffers (peer-mapped memory of
+// other GPUs included): the limb-sharded key-switch's all-gather fused into the transform that feeds it
+void launch_intt_to_peers(const DeviceTables& dt, BatchPtr in, const RowMap& map, u64* const* peers, int npeer, cudaStream_t s);
 
 // ---- basis extension (ModUp / ModDown / BFV scaling), Lattigo-style with float64 overflow count ----
 constexpr int kBexMaxSrc = 16;

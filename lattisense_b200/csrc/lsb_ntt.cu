@@ -281,6 +281,12 @@ void launch_ntt_finish(const DeviceTables& dt, BatchPtr b, const NttFinish& fin,
     launch_finish(dt, fin.a, b, fin.addend, fin.has_addend, fin.out, fin.fm_dev, fm.n, batch, s);
 }
 
+void launch_intt_to_peers(const DeviceTables& dt, BatchPtr in, const RowMap& map, u64* const* peers, int npeer,
+                          cudaStream_t s) {
+    if (map.n <= 0) return;
+    launch_ntt_cluster(dt, in, in, map, 1, true, dt.f64_ok, ntt_allow_f64(), s, nullptr, peers, npeer);
+}
+
 void launch_ntt(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap& map, int batch, bool inverse,
                 cudaStream_t s) {
     if (batch <= 0 || map.n <= 0) return;

@@ -41,6 +41,7 @@ struct ClusterCfg {
     static constexpr int G0 = BS / CL;      // cross-round groups per CTA
 };
 
+constexpr int kMaxPeers = 8;
 struct NttClArgs {
     BatchPtr in, out;
     int total_rows;
@@ -53,6 +54,11 @@ struct NttClArgs {
     const FinishMap* fm;
     BatchPtr fa, fadd, fout;
     int has_add;
+    // fused all-gather (inverse only, limb-sharded key-switch): instead of `out`, row r is stored at word offset
+    // out_slot[r] * N of EVERY buffer in peer[] (this rank's own copy included) -- peer-mapped device memory of the
+    // other ranks' GPUs, written over NVLink while the transform's remaining groups are still being computed
+    int npeer;
+    u64* peer[kMaxPeers];
 };
 
 template <int I, int NR, class F>
@@ -69,7 +75,7 @@ __device__ __forceinline__ const typename P::TW* tw_of(const NttClArgs& a, int m
     else return a.tw + (size_t)mod * N;
 }
 
-template <int LOGN, bool INV, class P, bool FIN>
+template <int LOGN, bool INV, class P, bool FIN, bool PEERS = false>
 __device__ __forceinline__ void ntt_cluster_body(const NttClArgs& a, u64* sm) {
     typedef ClusterCfg<LOGN> C;
     constexpr int N = C::N, CL = C::CL, BS = C::BS, NB = C::NB, TILE = C::TILE, NT = C::NT;
@@ -184,17 +190,26 @@ __device__ __forceinline__ void ntt_cluster_body(const NttClArgs& a, u64* sm) {
 #pragma unroll
             for (int k = 0; k < 16; k++) x[k] = P::from_bits(peer[k / NB][(k % NB) * BS + swz(g)]);
             inv_stages<P, 4, true>(x, tw, 1u, m, ninv, w_ninv);
+            if constexpr (!PEERS) {
 #pragma unroll
-            for (int k = 0; k < 16; k++) dst[g + k * BS] = P::inv_canonical(x[k], m);
+                for (int k = 0; k < 16; k++) dst[g + k * BS] = P::inv_canonical(x[k], m);
+            } else {
+                const size_t off = (size_t)a.map.out_slot[r] * N + g;
+#pragma unroll
+                for (int k = 0; k < 16; k++) {
+                    const u64 v = P::inv_canonical(x[k], m);
+                    for (int pr = 0; pr < a.npeer; pr++) a.peer[pr][off + k * BS] = v;
+                }
+            }
         }
         if (CL > 1) cluster.sync();  // peers may still be reading this CTA's shared memory
     }
 }
 
-template <int LOGN, bool INV, class P, bool FIN = false>
+template <int LOGN, bool INV, class P, bool FIN = false, bool PEERS = false>
 __global__ void __launch_bounds__(ClusterCfg<LOGN>::NT, LSB_CL_MINB) k_ntt_cluster(const __grid_constant__ NttClArgs a) {
     extern __shared__ __align__(1024) u64 sm[];
-    ntt_cluster_body<LOGN, INV, P, FIN>(a, sm);
+    ntt_cluster_body<LOGN, INV, P, FIN, PEERS>(a, sm);
 }
 
 template <int LOGN, class K>
@@ -222,6 +237,11 @@ static void launch_cluster_k(K kernel, const NttClArgs& a, cudaStream_t s) {
 
 template <int LOGN>
 static void launch_cluster_n(const NttClArgs& a, bool inverse, bool f64, cudaStream_t s) {
+    if (a.npeer > 0) {
+        if (f64) launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, true, ArithF64, false, true>, a, s);
+        else launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, true, ArithU64, false, true>, a, s);
+        return;
+    }
     if (a.fm) {
         if (f64) launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, false, ArithF64, true>, a, s);
         else launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, false, ArithU64, true>, a, s);
@@ -238,8 +258,11 @@ static void launch_cluster_n(const NttClArgs& a, bool inverse, bool f64, cudaStr
 
 // Rows whose prime qualifies for the FP64 policy and the others go in separate launches (CTA-uniform code).
 void launch_ntt_cluster(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap& map, int batch, bool inverse,
-                        const std::vector<uint8_t>& f64_ok, bool allow_f64, cudaStream_t s, const NttFinish* fin) {
+                        const std::vector<uint8_t>& f64_ok, bool allow_f64, cudaStream_t s, const NttFinish* fin,
+                        u64* const* peers, int npeer) {
     LSB_CHECK(!(fin && inverse), "lsb: the finish epilogue belongs to the forward transform");
+    LSB_CHECK(npeer == 0 || (inverse && !fin && batch == 1 && npeer <= kMaxPeers && peers),
+              "lsb: peer stores belong to the un-batched inverse transform (at most 8 peers)");
     RowMap parts[2];
     parts[0].n = parts[1].n = 0;
     for (int r = 0; r < map.n; r++) {
@@ -269,6 +292,8 @@ void launch_ntt_cluster(const DeviceTables& dt, BatchPtr in, BatchPtr out, const
             a.fa = a.fadd = a.fout = in;
             a.has_add = 0;
         }
+        a.npeer = npeer;
+        for (int pr = 0; pr < npeer; pr++) a.peer[pr] = peers[pr];
         ProfScope _ps(dt.prof, inverse ? PK_NTT_INV : PK_NTT_FWD, s, 16.0 * dt.N * a.total_rows, 1);
         switch (dt.logN) {
             case 12: launch_cluster_n<12>(a, inverse, f == 1, s); break;

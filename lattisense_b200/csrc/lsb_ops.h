@@ -52,9 +52,11 @@ void op_mult_relin_rescale(OpEnv& e, int level, BatchPtr a, BatchPtr b, const u6
 
 // limb-sharded key-switch phases (lsb_shard.cu; the all-gathers between them are the caller's)
 struct ShardPlan;
-void op_ks_shard_begin(OpEnv& e, const ShardPlan& sp, BatchPtr c_own_ntt, BatchPtr coeff_own, int batch);
+// `peers` (optional, world pointers): fused all-gather -- the phase's INTT stores into every rank's gathered buffer
+void op_ks_shard_begin(OpEnv& e, const ShardPlan& sp, BatchPtr c_own_ntt, BatchPtr coeff_own, int batch,
+                       u64* const* peers = nullptr);
 void op_ks_shard_inner(OpEnv& e, const ShardPlan& sp, BatchPtr coeff_all, BatchPtr c_own_ntt, const u64* evk_own,
-                       BatchPtr acc_own, BatchPtr accP_own, int batch);
+                       BatchPtr acc_own, BatchPtr accP_own, int batch, u64* const* peers = nullptr);
 void op_ks_shard_end(OpEnv& e, const ShardPlan& sp, BatchPtr accP_all, BatchPtr acc_own, BatchPtr addend_own, bool has_addend,
                      BatchPtr out_own, int batch);
 

@@ -123,22 +123,30 @@ const ShardPlan& Context::shard_plan(int level, int world, int rank) {
     return *it->second;
 }
 
-// phase 1: coeff_own[u] = INTT(c_own_ntt[u]) for the owned Q limbs
-void op_ks_shard_begin(OpEnv& e, const ShardPlan& sp, BatchPtr c_own_ntt, BatchPtr coeff_own, int batch) {
+// phase 1: coeff_own[u] = INTT(c_own_ntt[u]) for the owned Q limbs.  With `peers` (the coeff_all buffer of every
+// rank, peer-mapped) the transform stores its outputs straight into slot rank*cq + u of each of them: the first
+// all-gather happens inside the INTT kernel, over NVLink, and coeff_own is not written.
+void op_ks_shard_begin(OpEnv& e, const ShardPlan& sp, BatchPtr c_own_ntt, BatchPtr coeff_own, int batch, u64* const* peers) {
     LSB_CUDA(cudaSetDevice(e.c.device));
     if (sp.nq_own == 0) return;
     RowMap m;
     m.n = sp.nq_own;
     for (int u = 0; u < sp.nq_own; u++) {
-        m.in_slot[u] = m.out_slot[u] = (uint8_t)u;
+        m.in_slot[u] = (uint8_t)u;
+        m.out_slot[u] = (uint8_t)(peers ? sp.rank * sp.cq + u : u);
         m.mod[u] = (uint8_t)sp.own_q[u];
     }
-    launch_ntt(e.c.dt, c_own_ntt, coeff_own, m, batch, true, e.s);
+    if (peers) {
+        LSB_CHECK(batch == 1, "lsb: the fused all-gather handles one ciphertext per call");
+        launch_intt_to_peers(e.c.dt, c_own_ntt, m, peers, sp.world, e.s);
+    } else {
+        launch_ntt(e.c.dt, c_own_ntt, coeff_own, m, batch, true, e.s);
+    }
 }
 
 // phase 2: ModUp to the owned targets, NTT, inner product with the owned key limbs, INTT of the owned P accumulators
 void op_ks_shard_inner(OpEnv& e, const ShardPlan& sp, BatchPtr coeff_all, BatchPtr c_own_ntt, const u64* evk_own,
-                       BatchPtr acc_own, BatchPtr accP_own, int batch) {
+                       BatchPtr acc_own, BatchPtr accP_own, int batch, u64* const* peers) {
     Context& c = e.c;
     LSB_CUDA(cudaSetDevice(c.device));
     if (sp.n_own == 0) return;
@@ -180,11 +188,16 @@ void op_ks_shard_inner(OpEnv& e, const ShardPlan& sp, BatchPtr coeff_all, BatchP
         for (int p = 0; p < 2; p++)
             for (int u = 0; u < sp.np_own; u++) {
                 m.in_slot[m.n] = (uint8_t)(p * sp.n_own + sp.nq_own + u);
-                m.out_slot[m.n] = (uint8_t)(p * sp.cp + u);
+                m.out_slot[m.n] = (uint8_t)(peers ? (sp.rank * 2 + p) * sp.cp + u : p * sp.cp + u);
                 m.mod[m.n] = (uint8_t)c.idxP(sp.own_p[u]);
                 m.n++;
             }
-        launch_ntt(c.dt, acc_own, accP_own, m, batch, true, e.s);
+        if (peers) {  // second all-gather fused into the INTT of the owned P accumulators (peers = every accP_all)
+            LSB_CHECK(batch == 1, "lsb: the fused all-gather handles one ciphertext per call");
+            launch_intt_to_peers(c.dt, acc_own, m, peers, sp.world, e.s);
+        } else {
+            launch_ntt(c.dt, acc_own, accP_own, m, batch, true, e.s);
+        }
     }
 }
 

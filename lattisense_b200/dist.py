@@ -154,6 +154,52 @@ class ShardedKeySwitch:
                                           self.acc_own.data_ptr(), addend_own.data_ptr() if addend_own is not None else None,
                                           out_own.data_ptr(), 1, self._stream()))
 
+    # ---- fused compute + collective: the INTT kernels store into every rank's gathered buffer over peer memory ----
+    def enable_p2p(self, group=None):
+        """Re-home coeff_all / accP_all in torch symmetric memory and exchange the peer mappings (NVLink P2P).
+        After this, run_p2p() needs no NCCL collective: only two cross-rank barriers per key-switch."""
+        import torch.distributed._symmetric_memory as symm_mem
+        n_c, n_p = self.coeff_all.numel(), self.accP_all.numel()
+        buf = symm_mem.empty((n_c + n_p,), dtype=torch.int64, device=self.device)
+        buf.zero_()
+        group = group or dist.group.WORLD
+        self._symm = symm_mem.rendezvous(buf, group.group_name)
+        self._symm_buf = buf
+        self.coeff_all = buf[:n_c].view(self.coeff_all.shape)
+        self.accP_all = buf[n_c:].view(self.accP_all.shape)
+        self.set_peers([int(p) for p in self._symm.buffer_ptrs], [int(p) + 8 * n_c for p in self._symm.buffer_ptrs])
+        self._barrier = lambda ch: self._symm.barrier(channel=ch)
+
+    def set_peers(self, coeff_ptrs, accp_ptrs, barrier=None):
+        """peer tables: device pointers of every rank's coeff_all / accP_all as mapped in this process"""
+        C = self.C
+        self._peer_c = (C.c_void_p * self.world)(*coeff_ptrs)
+        self._peer_p = (C.c_void_p * self.world)(*accp_ptrs)
+        if barrier is not None:
+            self._barrier = barrier
+
+    def begin_p2p(self, c_own_ntt):
+        L = self.L
+        L._check(L.lib().lsb_ks_shard_begin_p2p(self.ctx.h, self.level, self.world, self.rank, c_own_ntt.data_ptr(),
+                                                self._peer_c, self._stream()))
+
+    def inner_p2p(self, c_own_ntt, evk_own):
+        L = self.L
+        L._check(L.lib().lsb_ks_shard_inner_p2p(self.ctx.h, self.level, self.world, self.rank, self.coeff_all.data_ptr(),
+                                                c_own_ntt.data_ptr(), evk_own.data_ptr(), self.acc_own.data_ptr(),
+                                                self._peer_p, self._stream()))
+
+    def run_p2p(self, c_own_ntt, evk_own, addend_own=None):
+        """same result as run(); barrier 0 also keeps a fast rank's next phase-2 stores out of accP_all while a slow
+        rank still reads it in phase 3, barrier 1 does the same for coeff_all"""
+        out = torch.empty((2, max(self.nq_own, 1), self.ctx.N), dtype=torch.int64, device=self.device)
+        self.begin_p2p(c_own_ntt)
+        self._barrier(0)
+        self.inner_p2p(c_own_ntt, evk_own)
+        self._barrier(1)
+        self.end(addend_own, out)
+        return out[:, :self.nq_own]
+
     def run(self, c_own_ntt, evk_own, addend_own=None):
         """c_own_ntt [nq_own][N], evk_own [beta][2][n_own][N], addend_own [2][nq_own][N] (int64 views of u64 residues,
         on this rank's GPU) -> out_own [2][nq_own][N]"""

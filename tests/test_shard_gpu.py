@@ -31,23 +31,28 @@ def _dev(a):
     return torch.from_numpy(np.ascontiguousarray(a).view(np.int64)).cuda()
 
 
-def _run_emulated(ctx, params, level, world, ct3, evk, with_addend):
+def _run_emulated(ctx, params, level, world, ct3, evk, with_addend, p2p=False):
     ranks = [ShardedKeySwitch(ctx, level, world, r, gather=lambda a, b: None) for r in range(world)]
+    if p2p:  # fused all-gather: every rank's INTT kernels store into all ranks' gathered buffers (here: same GPU)
+        for sk in ranks:
+            sk.set_peers([x.coeff_all.data_ptr() for x in ranks], [x.accP_all.data_ptr() for x in ranks])
     c_own = [_dev(shard_poly(ct3[2], sk.own_q)) if sk.nq_own else torch.zeros((1, ctx.N), dtype=torch.int64).cuda()
              for sk in ranks]
     evk_own = [_dev(shard_evk(evk, level, params.k, sk.own_q, sk.own_p)) if sk.n_own else None for sk in ranks]
     add_own = [_dev(shard_poly(ct3[:2], sk.own_q)) if (with_addend and sk.nq_own) else None for sk in ranks]
     for sk, c in zip(ranks, c_own):
-        sk.begin(c)
+        sk.begin_p2p(c) if p2p else sk.begin(c)
     coeff_all = torch.stack([sk.coeff_own for sk in ranks])
     for sk, c, e in zip(ranks, c_own, evk_own):
-        sk.coeff_all.copy_(coeff_all)
+        if not p2p:
+            sk.coeff_all.copy_(coeff_all)
         if sk.n_own:
-            sk.inner(c, e)
+            sk.inner_p2p(c, e) if p2p else sk.inner(c, e)
     accp_all = torch.stack([sk.accP_own for sk in ranks])
     parts = []
     for sk, a in zip(ranks, add_own):
-        sk.accP_all.copy_(accp_all)
+        if not p2p:
+            sk.accP_all.copy_(accp_all)
         out = torch.zeros((2, max(sk.nq_own, 1), ctx.N), dtype=torch.int64).cuda()
         if sk.nq_own:
             sk.end(a, out)
@@ -71,6 +76,8 @@ def test_sharded_relin_matches_oracle(params, level, world):
     want = o.relin(ct3, evk)
     got = _run_emulated(ctx, params, level, world, ct3, evk, True)
     assert np.array_equal(got, want)
+    # the all-gathers fused into the INTT kernels (stores into every rank's gathered buffer)
+    assert np.array_equal(_run_emulated(ctx, params, level, world, ct3, evk, True, p2p=True), want)
     # without the (c0, c1) addend: the bare key-switch of c2 (what a rotation adds c0 to)
     ct3z = ct3.copy()
     ct3z[:2] = 0

@@ -48,6 +48,23 @@ for _ in range(reps):
 ev1.record()
 torch.cuda.synchronize()
 ms_shard = rk.max(ev0.elapsed_time(ev1) / reps)
+# fused compute + collective: INTT kernels store into the peers' buffers over NVLink, two barriers, no NCCL collective
+ms_p2p, p2p_same = None, None
+if rk.world > 1 and os.environ.get("KS_P2P", "1") == "1":
+    sk.enable_p2p()
+    out2 = sk.run_p2p(c_own, evk_own, add_own)
+    torch.cuda.synchronize()
+    p2p_same = bool(torch.equal(out2, out))
+    for _ in range(5):
+        sk.run_p2p(c_own, evk_own, add_own)
+    rk.barrier()
+    ev0.record()
+    for _ in range(reps):
+        sk.run_p2p(c_own, evk_own, add_own)
+    ev1.record()
+    torch.cuda.synchronize()
+    ms_p2p = rk.max(ev0.elapsed_time(ev1) / reps)
+    p2p_same = rk.sum(1.0 if p2p_same else 0.0) == rk.world
 oks = rk.sum(1.0 if ok in (None, True) else 0.0)
 single = None
 if rk.rank == 0:
@@ -65,6 +82,7 @@ if rk.rank == 0:
     same = bool(torch.equal(o2[:, sk.own_q, :], out))
     print(json.dumps({"workload": "CKKS relinearisation key-switch n=2^%d level %d (l=%d, k=%d, beta=%d)" % (logN, level, l, k, beta),
                       "n_gpus": rk.world, "ms_sharded_max_over_ranks": ms_shard, "ms_single_gpu": single,
+                      "ms_sharded_fused_p2p": ms_p2p, "fused_equals_nccl_path_on_all_ranks": p2p_same,
                       "speedup": single / ms_shard, "ranks_bit_exact_vs_oracle": int(oks) if check else None,
                       "rank0_limbs_equal_single_gpu": same,
                       "evk_bytes_per_gpu": int(evk_own.numel() * 8), "evk_bytes_total": int(evk.size * 8),

@@ -1308,7 +1308,12 @@ static int run_task(GpuTask& task, CArgument* input_args, uint64_t n_in, CArgume
     TaskGraph& g = *task.graph;
     std::vector<int> devs = task.devices.empty() ? std::vector<int>{gpu_device} : task.devices;
     const int hw = (int)std::thread::hardware_concurrency();
-    const int nthreads = std::max(2, std::min(16, hw > 0 ? hw : 4) - 1);
+    // worker threads: min(16, cores) - 1 like the reference's pool cap (cpu_wrapper.cpp:57), shared fairly when several
+    // ranks run on one node (torchrun exports LOCAL_WORLD_SIZE); LSB_HOST_THREADS overrides
+    int share = hw > 0 ? hw : 4;
+    if (const char* lw = getenv("LOCAL_WORLD_SIZE")) share = std::max(2, share / std::max(1, atoi(lw)));
+    int nthreads = std::max(2, std::min(16, share) - 1);
+    if (const char* ht = getenv("LSB_HOST_THREADS")) nthreads = std::max(1, atoi(ht));
     static WorkerPool pool(nthreads);  // shared by all tasks of the process
     RunState rs(task, pool, cb, ud);
     long long launches0 = 0;

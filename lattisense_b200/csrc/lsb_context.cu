@@ -83,6 +83,8 @@ Context::Context(int device_, int scheme_, int logN_, const u64* q, int nq_, con
     dt.tw_inv = (const Tw*)to_device(inv.data(), inv.size() * sizeof(Tw));
     dt.f64_ok.resize(nmod);
     for (int m = 0; m < nmod; m++) dt.f64_ok[m] = (uint8_t)mc[m].f64_ok;
+    dt.elem_f64_ok.resize(nmod);
+    for (int m = 0; m < nmod; m++) dt.elem_f64_ok[m] = moduli[m] < kElemF64Limit ? 1 : 0;
     dt.tw_fwd_d = (const TwD*)to_device(fwd_d.data(), fwd_d.size() * sizeof(TwD));
     dt.tw_inv_d = (const TwD*)to_device(inv_d.data(), inv_d.size() * sizeof(TwD));
     dt.mods = (const ModConst*)to_device(mc.data(), mc.size() * sizeof(ModConst));

@@ -12,6 +12,14 @@ namespace lsb {
 
 constexpr int kElemThreads = 256;
 
+static bool elem_f64_enabled() {  // LSB_ELEM_F64=0: integer arithmetic in every element-wise kernel (A/B switch)
+    static const bool v = [] {
+        const char* e = getenv("LSB_ELEM_F64");
+        return !(e && atoi(e) == 0);
+    }();
+    return v;
+}
+
 static inline dim3 elem_grid(int N, int rows, int batch) { return dim3((N / 2 + kElemThreads - 1) / kElemThreads, rows, batch); }
 
 __device__ __forceinline__ W2 ld2(const u64* p, int j2) { return reinterpret_cast<const W2*>(p)[j2]; }
@@ -84,11 +92,13 @@ struct TensorArgs {
     const ModConst* mods;
     uint8_t mod[64];
 };
+template <bool F64>
 __global__ void __launch_bounds__(kElemThreads) k_tensor(const __grid_constant__ TensorArgs g) {
     const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
     if (j2 >= g.N / 2) return;
     const int i = blockIdx.y, b = blockIdx.z;
-    const BarrettQ bq = g.mods[g.mod[i]].bq;
+    const ModConst& mc = g.mods[g.mod[i]];
+    const BarrettQ bq = mc.bq;
     const u64 q = bq.q;
     const u64* pa = g.a.at(b);
     const u64* pb = g.b.at(b);
@@ -97,6 +107,23 @@ __global__ void __launch_bounds__(kElemThreads) k_tensor(const __grid_constant__
     const W2 a0 = ld2(pa + (size_t)i * N, j2), a1 = ld2(pa + (size_t)(g.in_ps + i) * N, j2);
     const W2 b0 = ld2(pb + (size_t)i * N, j2), b1 = ld2(pb + (size_t)(g.in_ps + i) * N, j2);
     W2 c0, c1, c2;
+    if constexpr (F64) {
+        // primes below 2^47: the four products per coefficient on the FP64 pipe (the integer version is bound by IMAD,
+        // profiles/r01_step_kernels_ncu.txt); |a0 b1 + a1 b0| <= 3 q before the canonical reduction
+        const double qd = mc.qd, qi = mc.qinvd;
+        const double x0a = f64_from_u64(a0.a), x0b = f64_from_u64(a0.b), x1a = f64_from_u64(a1.a), x1b = f64_from_u64(a1.b);
+        const double y0a = f64_from_u64(b0.a), y0b = f64_from_u64(b0.b), y1a = f64_from_u64(b1.a), y1b = f64_from_u64(b1.b);
+        c0.a = f64_canon_u(f64_mulmod_var(x0a, y0a, qd, qi), qd, qi);
+        c0.b = f64_canon_u(f64_mulmod_var(x0b, y0b, qd, qi), qd, qi);
+        c2.a = f64_canon_u(f64_mulmod_var(x1a, y1a, qd, qi), qd, qi);
+        c2.b = f64_canon_u(f64_mulmod_var(x1b, y1b, qd, qi), qd, qi);
+        c1.a = f64_canon_u(d_add(f64_mulmod_var(x0a, y1a, qd, qi), f64_mulmod_var(x1a, y0a, qd, qi)), qd, qi);
+        c1.b = f64_canon_u(d_add(f64_mulmod_var(x0b, y1b, qd, qi), f64_mulmod_var(x1b, y0b, qd, qi)), qd, qi);
+        st2(po + (size_t)i * N, j2, c0);
+        st2(po + (size_t)(g.out_ps + i) * N, j2, c1);
+        st2(po + (size_t)(2 * g.out_ps + i) * N, j2, c2);
+        return;
+    }
     c0.a = mulmod(a0.a, b0.a, bq);
     c0.b = mulmod(a0.b, b0.b, bq);
     c2.a = mulmod(a1.a, b1.a, bq);
@@ -129,9 +156,14 @@ void launch_tensor(const DeviceTables& dt, BatchPtr a, BatchPtr b, BatchPtr out,
     g.in_ps = a_poly_stride;
     g.out_ps = out_poly_stride;
     g.mods = dt.mods;
-    for (int i = 0; i < nl; i++) g.mod[i] = mod_of_limb[i];
+    bool f64 = elem_f64_enabled();
+    for (int i = 0; i < nl; i++) {
+        g.mod[i] = mod_of_limb[i];
+        f64 = f64 && dt.elem_f64_ok[mod_of_limb[i]];
+    }
     ProfScope _ps(dt.prof, PK_ELEMWISE, s, 8.0 * dt.N * nl * batch * 7);
-    k_tensor<<<elem_grid(dt.N, nl, batch), kElemThreads, 0, s>>>(g);
+    if (f64) k_tensor<true><<<elem_grid(dt.N, nl, batch), kElemThreads, 0, s>>>(g);
+    else k_tensor<false><<<elem_grid(dt.N, nl, batch), kElemThreads, 0, s>>>(g);
     LSB_CUDA(cudaGetLastError());
 }
 
@@ -336,15 +368,15 @@ struct KsInnerK {
     int N;
     const ModConst* mods;
 };
-template <bool F64>
+template <bool F64, bool MAPPED>
 __global__ void __launch_bounds__(kElemThreads) k_ks_inner(const __grid_constant__ KsInnerK g) {
     const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
     if (j2 >= g.N / 2) return;
     const KsInnerArgs& a = g.a;
     const int row = blockIdx.y, b = blockIdx.z;
-    const int t = a.mapped ? a.tmap[row] : row;
-    const int lk = a.mapped ? a.rows : a.l + a.k, klimbs = a.mapped ? a.rows : a.key_level + 1 + a.k;
-    const int key_limb = a.mapped ? row : (t < a.l ? t : a.key_level + 1 + (t - a.l));
+    const int t = MAPPED ? a.tmap[row] : row;
+    const int lk = MAPPED ? a.rows : a.l + a.k, klimbs = MAPPED ? a.rows : a.key_level + 1 + a.k;
+    const int key_limb = MAPPED ? row : (t < a.l ? t : a.key_level + 1 + (t - a.l));
     const ModConst& mc = g.mods[t < a.l ? t : a.nq + (t - a.l)];
     const size_t N = g.N;
     const u64* pext = a.ext.at(b);
@@ -409,8 +441,15 @@ void launch_ks_inner(const DeviceTables& dt, const KsInnerArgs& a, int batch, cu
     ProfScope _ps(dt.prof, PK_KS_INNER, s, 8.0 * dt.N * (a.l + a.k) * (batch * (a.beta + 2.0) + 2.0 * a.beta));
     const int rows = a.mapped ? a.rows : a.l + a.k;
     if (rows <= 0) return;
-    if (a.f64 && a.beta <= 16) k_ks_inner<true><<<elem_grid(dt.N, rows, batch), kElemThreads, 0, s>>>(g);
-    else k_ks_inner<false><<<elem_grid(dt.N, rows, batch), kElemThreads, 0, s>>>(g);
+    const dim3 grid = elem_grid(dt.N, rows, batch);
+    const bool f64 = a.f64 && a.beta <= 16;
+    if (a.mapped) {
+        if (f64) k_ks_inner<true, true><<<grid, kElemThreads, 0, s>>>(g);
+        else k_ks_inner<false, true><<<grid, kElemThreads, 0, s>>>(g);
+    } else {
+        if (f64) k_ks_inner<true, false><<<grid, kElemThreads, 0, s>>>(g);
+        else k_ks_inner<false, false><<<grid, kElemThreads, 0, s>>>(g);
+    }
     LSB_CUDA(cudaGetLastError());
 }
 

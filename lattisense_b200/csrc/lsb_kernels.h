@@ -15,6 +15,7 @@ struct DeviceTables {
     const Tw* tw_inv = nullptr;  // [nmod][N]  psi^-bitrev(i)
     const TwD* tw_fwd_d = nullptr;  // FP64 policy: (w, w/q) pairs, zero for ineligible primes
     const TwD* tw_inv_d = nullptr;
+    std::vector<uint8_t> elem_f64_ok;  // per modulus: below 2^47, element-wise kernels may use the FP64 pipe
     // the same tables with the stages of the cluster kernel's last round in tail-SoA order (lsb_ntt_arith.h)
     const Tw* twc_fwd = nullptr;
     const Tw* twc_inv = nullptr;

@@ -384,6 +384,66 @@ def run_ours(args):
                                                 stream)), reps)
     ntt_alone = 16.0 * N * 2 * l * B * reps / (ms_ntt / 1e3) / 1e9
 
+    # the rest of BASELINE.json's metric ("mult_relin + rotate ops/s, N=2^14..2^16"): device-resident side numbers,
+    # same timing rules, single GPU only (parity of these paths: tests/test_gpu_parity.py, tests/test_runner_gpu.py)
+    secondary = None
+    if world == 1 and not args.no_secondary:
+        secondary = {}
+
+        def rate(fn, units, steps=5):
+            for _ in range(3):
+                fn()
+            return units * steps / (timed(fn, steps) / 1e3)
+
+        # CKKS rotate (automorphism + key-switch), same ring / level / batch as the headline
+        gal = R.galois_for_col_step(N, 1)
+        glk_dev = rand_limbs((P.beta(LEVEL), 2), P.q[:l] + P.p)
+        rot_out = torch.empty((B, 2, l, N), dtype=torch.int64, device=dev)
+        secondary["ckks_rotate_n16384_level3_ops_per_s"] = rate(lambda: L._check(lib.lsb_rotate(
+            ctx.h, LEVEL, a_dev.data_ptr(), glk_dev.data_ptr(), LEVEL, gal, rot_out.data_ptr(), B, stream)), B)
+        del glk_dev, rot_out
+        # BFV mult_relin (configs[0]: n=16384, t=65537, level 2): 54-57-bit primes -> integer NTT policy
+        PB, lb, Bb = R.BFV_N14, 3, 256
+        cb = L.Context(PB.scheme, PB.logN, PB.q, PB.p, PB.t, device=local)
+        cb.stream = stream
+
+        def limbs(lead, mods, n):
+            t = torch.empty(lead + (len(mods), n), dtype=torch.int64, device=dev)
+            for i, m in enumerate(mods):
+                t[..., i, :] = torch.randint(0, m, lead + (n,), dtype=torch.int64, device=dev)
+            return t
+
+        xa, xb = limbs((Bb, 2), PB.q[:lb], PB.N), limbs((Bb, 2), PB.q[:lb], PB.N)
+        rk = limbs((PB.beta(lb - 1), 2), PB.q[:lb] + PB.p, PB.N)
+        xo = torch.empty((Bb, 2, lb, PB.N), dtype=torch.int64, device=dev)
+        secondary["bfv_mult_relin_n16384_level2_ops_per_s"] = rate(lambda: L._check(lib.lsb_mult_relin(
+            cb.h, lb - 1, xa.data_ptr(), xb.data_ptr(), rk.data_ptr(), lb - 1, xo.data_ptr(), Bb, stream)), Bb)
+        del xa, xb, rk, xo
+        cb.close()
+        # CKKS N=2^16 (bootstrap chain: 61-bit and 40-bit primes, k=5): rotations at level 2 (configs[3]) and one
+        # full-depth relinearisation key-switch (level 24, beta=5: the unit configs[4] is made of)
+        P16 = R.CKKS_BTP_N16
+        c16 = L.Context(P16.scheme, P16.logN, P16.q, P16.p, 0, device=local)
+        c16.stream = stream
+        l16, B16 = 3, 64
+        ct = limbs((B16, 2), P16.q[:l16], P16.N)
+        gk = limbs((P16.beta(l16 - 1), 2), P16.q[:l16] + P16.p, P16.N)
+        ro = torch.empty_like(ct)
+        g16 = R.galois_for_col_step(P16.N, 1)
+        secondary["ckks_rotate_n65536_level2_ops_per_s"] = rate(lambda: L._check(lib.lsb_rotate(
+            c16.h, l16 - 1, ct.data_ptr(), gk.data_ptr(), l16 - 1, g16, ro.data_ptr(), B16, stream)), B16)
+        del ct, gk, ro
+        l25, B25 = 25, 8
+        c3 = limbs((B25, 3), P16.q[:l25], P16.N)
+        rk = limbs((P16.beta(l25 - 1), 2), P16.q[:l25] + P16.p, P16.N)
+        o2 = torch.empty((B25, 2, l25, P16.N), dtype=torch.int64, device=dev)
+        secondary["ckks_keyswitch_n65536_level24_ops_per_s"] = rate(lambda: L._check(lib.lsb_relin(
+            c16.h, l25 - 1, c3.data_ptr(), rk.data_ptr(), l25 - 1, o2.data_ptr(), B25, stream)), B25)
+        del c3, rk, o2
+        c16.close()
+        secondary["note"] = ("device-resident, CUDA events, batches 1024 / 256 / 64 / 8; random residues (throughput does "
+                             "not depend on values)")
+
     if rank != 0:
         return
     cores = len(os.sched_getaffinity(0))
@@ -418,6 +478,7 @@ def run_ours(args):
                      "share_of_step": ntt_ms / tot_ms if tot_ms else None,
                      "standalone_ntt_gbs": ntt_alone, "standalone_frac": ntt_alone / peak},
         "kernel_ms_per_step": {k: v[0] for k, v in prof.items()},
+        "secondary": secondary,
         "cpu_baseline": cpu,
     }
     print(json.dumps(line), flush=True)
@@ -432,6 +493,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-api", action="store_true", help="skip the run_fhe_gpu_task end-to-end leg")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the rotate / BFV / N=2^16 side measurements")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -25,6 +25,18 @@
 #ifndef LSB_CL_NT
 #define LSB_CL_NT 256
 #endif
+// N = 2^14 (the headline ring): 8 CTAs of 128 threads and 16 KiB per limb, 8 resident per SM.  Measured against the
+// other shapes with the same 32 warps per SM (tools/ab_ntt.sh): 4 CTAs x 256 threads 2599 / 2321 GB/s (fwd / inv),
+// 2 x 256 at 3 per SM 2767 / 2466, 8 x 128 2745 / 2492.
+#ifndef LSB_CL14
+#define LSB_CL14 8
+#endif
+#ifndef LSB_CL14_NT
+#define LSB_CL14_NT 128
+#endif
+#ifndef LSB_CL14_MINB
+#define LSB_CL14_MINB 8
+#endif
 namespace cg = cooperative_groups;
 
 namespace lsb {
@@ -32,12 +44,13 @@ namespace lsb {
 template <int LOGN>
 struct ClusterCfg {
     static constexpr int N = 1 << LOGN;
-    static constexpr int CL = LOGN <= 12 ? 1 : LOGN == 13 ? 2 : LOGN == 14 ? 4 : 8;  // CTAs per limb
+    static constexpr int CL = LOGN <= 12 ? 1 : LOGN == 13 ? 2 : LOGN == 14 ? LSB_CL14 : 8;  // CTAs per limb
     static constexpr int BS = N / 16;                                                 // block = sub-transform size
     static constexpr int LS = LOGN - 4;
     static constexpr int NB = 16 / CL;      // blocks per CTA
     static constexpr int TILE = N / CL;     // words of shared memory per CTA
-    static constexpr int NT = LSB_CL_NT;
+    static constexpr int NT = LOGN == 14 ? LSB_CL14_NT : LSB_CL_NT;
+    static constexpr int MINB = LOGN == 14 ? LSB_CL14_MINB : LSB_CL_MINB;  // resident CTAs per SM asked of ptxas
     static constexpr int G0 = BS / CL;      // cross-round groups per CTA
 };
 
@@ -207,7 +220,7 @@ __device__ __forceinline__ void ntt_cluster_body(const NttClArgs& a, u64* sm) {
 }
 
 template <int LOGN, bool INV, class P, bool FIN = false, bool PEERS = false>
-__global__ void __launch_bounds__(ClusterCfg<LOGN>::NT, LSB_CL_MINB) k_ntt_cluster(const __grid_constant__ NttClArgs a) {
+__global__ void __launch_bounds__(ClusterCfg<LOGN>::NT, ClusterCfg<LOGN>::MINB) k_ntt_cluster(const __grid_constant__ NttClArgs a) {
     extern __shared__ __align__(1024) u64 sm[];
     ntt_cluster_body<LOGN, INV, P, FIN, PEERS>(a, sm);
 }

@@ -4,7 +4,7 @@
 //   [INTT c] -> ModUp (beta digits, Lattigo float-v CRT) -> NTT of the extended limbs ->
 //   inner product with the evaluation key -> INTT of the 2k P-limbs -> ModDown extension ->
 //   NTT -> (acc - ext) * P^-1 (+ c0/c1).
-// A batch is processed in chunks bounded by the scratch budget (LSB_SCRATCH_MB, default 4 GiB): measured
+// A batch is processed in chunks bounded by the scratch budget (LSB_SCRATCH_MB, default 8 GiB): measured
 // on B200 (profiles/r01_scratch_sweep.txt) large launches beat L2-resident small chunks 2:1 because
 // the kernels are integer-pipe bound and small launches leave SMs idle at the tail.
 #include <cstdlib>
@@ -22,7 +22,7 @@ static BatchPtr adv(BatchPtr p, int b0) {
 static size_t scratch_budget_words() {
     static size_t v = [] {
         const char* e = getenv("LSB_SCRATCH_MB");
-        size_t mb = e ? (size_t)atol(e) : 4096;
+        size_t mb = e ? (size_t)atol(e) : 8192;
         if (mb < 8) mb = 8;
         return mb * (1u << 20) / 8;
     }();

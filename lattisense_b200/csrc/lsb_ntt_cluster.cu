@@ -50,7 +50,9 @@ struct ClusterCfg {
     static constexpr int NB = 16 / CL;      // blocks per CTA
     static constexpr int TILE = N / CL;     // words of shared memory per CTA
     static constexpr int NT = LOGN == 14 ? LSB_CL14_NT : LSB_CL_NT;
-    static constexpr int MINB = LOGN == 14 ? LSB_CL14_MINB : LSB_CL_MINB;  // resident CTAs per SM asked of ptxas
+    // resident CTAs per SM asked of ptxas; N = 2^16 tiles are 64 KiB, so only 3 fit anyway and asking for 3 leaves the
+    // compiler 85 registers (inverse: 1365 -> 1538 GB/s on the mixed chain, 1004 -> 1098 GB/s on 61-bit primes)
+    static constexpr int MINB = LOGN == 14 ? LSB_CL14_MINB : LOGN == 16 ? 3 : LSB_CL_MINB;
     static constexpr int G0 = BS / CL;      // cross-round groups per CTA
 };
 

@@ -460,6 +460,7 @@ struct RescaleLiftArgs {
     const ModConst* mods;
 };
 // last: coefficient-domain limb `level` of each polynomial (block [npoly] with stride last_ps limbs)
+template <bool F64>
 __global__ void __launch_bounds__(kElemThreads) k_rescale_lift(const __grid_constant__ RescaleLiftArgs g) {
     const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
     if (j2 >= g.N / 2) return;
@@ -469,6 +470,18 @@ __global__ void __launch_bounds__(kElemThreads) k_rescale_lift(const __grid_cons
     x.a = addmod(x.a, half, ql);
     x.b = addmod(x.b, half, ql);
     u64* pt = g.tmp.at(b) + (size_t)p * g.level * g.N;
+    if constexpr (F64) {  // every prime below 2^47: the per-target reductions on the FP64 pipe (integer version: IMAD-bound)
+        const double xa = f64_from_u64(x.a), xb = f64_from_u64(x.b);
+        for (int i = 0; i < g.level; i++) {
+            const ModConst& m = g.mods[i];
+            const double hq = f64_from_u64(barrett64(half, m.bq));  // CTA-uniform
+            W2 o;
+            o.a = f64_canon_u(d_add(f64_centre(xa, m.qd, m.qinvd), -hq), m.qd, m.qinvd);
+            o.b = f64_canon_u(d_add(f64_centre(xb, m.qd, m.qinvd), -hq), m.qd, m.qinvd);
+            st2(pt + (size_t)i * g.N, j2, o);
+        }
+        return;
+    }
     for (int i = 0; i < g.level; i++) {
         const ModConst& m = g.mods[i];
         const u64 hq = barrett64(half, m.bq);  // CTA-uniform
@@ -483,7 +496,10 @@ void launch_rescale_lift(const DeviceTables& dt, BatchPtr last, int last_poly_st
     if (batch <= 0) return;
     RescaleLiftArgs g{last, tmp, dt.N, npoly, level, last_poly_stride, dt.mods};
     ProfScope _ps(dt.prof, PK_ELEMWISE, s, 8.0 * dt.N * npoly * batch * (1 + level));
-    k_rescale_lift<<<elem_grid(dt.N, npoly, batch), kElemThreads, 0, s>>>(g);
+    bool f64 = elem_f64_enabled();
+    for (int i = 0; i <= level; i++) f64 = f64 && dt.elem_f64_ok[i];
+    if (f64) k_rescale_lift<true><<<elem_grid(dt.N, npoly, batch), kElemThreads, 0, s>>>(g);
+    else k_rescale_lift<false><<<elem_grid(dt.N, npoly, batch), kElemThreads, 0, s>>>(g);
     LSB_CUDA(cudaGetLastError());
 }
 

@@ -190,8 +190,66 @@ def gen_configs():
          [Argument("out", o)])
 
 
+def two_sided(x, reach, unit):
+    """x rotated by -reach*unit .. +reach*unit (x itself in the middle)."""
+    steps = [-i * unit for i in range(1, reach + 1)] + [i * unit for i in range(1, reach + 1)]
+    r = rotate_cols(x, steps) if steps else []
+    return list(reversed(r[:reach])) + [x] + r[reach:]
+
+
+def gen_conv(case, shape, kernel, level=2):
+    """Single-channel packed 2-D convolution as the reference's rotation benchmark builds it
+    (examples/benchmark_convolution/benchmark_convolution.py:44-161): the input ciphertext holds
+    pack = slots/(h*w) channels; every channel offset and every kernel tap is one rotate_cols, every
+    tap a ct x pt product, all summed, rescaled, bias added.  (4,4)x(5,5) is SURVEY 8f-3's 38 400-node
+    scheduler / rotation stress graph."""
+    set_fhe_param(CkksParam.create_default_param(n=16384))
+    h, w = shape
+    kh, kw = kernel
+    pack = (16384 // 2) // (h * w)
+    x = CkksCiphertextNode("input_0_0", level=level)
+    wts = [[CkksPlaintextNode(f"w_{c}_{k}", level) for k in range(kh * kw)] for c in range(pack)]
+    bias = CkksPlaintextNode("b_0", level - 1)
+    chans = [x] + (rotate_cols(x, [i * h * w for i in range(1, pack)]) if pack > 1 else [])
+    acc = None
+    for c, xc in enumerate(chans):
+        taps = []
+        for r in two_sided(xc, kw // 2, w):
+            taps += two_sided(r, kh // 2, 1)
+        for k, tap in enumerate(taps):
+            prod = mult(tap, wts[c][k])
+            acc = prod if acc is None else add(acc, prod)
+    y = add(rescale(acc), bias, "y")
+    emit(case, [Argument("input_0", [x]), Argument("w", wts), Argument("b", [bias])], [Argument("output", [y])])
+
+
+def gen_logreg_n65536():
+    """cfg4 at the ring degree BASELINE.json quotes it on (N=2^16): same node pattern as cfg4_ckks_logreg, moduli of
+    CkksBtpParam.create_default_param() (frontend/custom_task.py:387-420; 25 Q + 5 P limbs, the graph uses level 3)."""
+    set_fhe_param(CkksBtpParam.create_default_param())
+    level = 3
+    xe = CkksCiphertextNode("x", level)
+    w = CkksPlaintextRingtNode("w")
+    b = CkksPlaintextNode("b", level - 1)
+    s = rescale(mult(xe, w))
+    for st in (16, 8, 4, 2, 1):
+        s = add(s, rotate_cols(s, st)[0])
+    s = add(s, b)
+    half = CkksPlaintextRingtNode("half")
+    o = rescale(mult(s, half), "out")
+    emit("cfg4_ckks_logreg_n65536", [Argument("x", xe), Argument("w", w), Argument("b", b), Argument("half", half)],
+         [Argument("out", o)])
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if sys.argv[1:] == ["n65536"]:
+        gen_logreg_n65536()
+        sys.exit(0)
+    if sys.argv[1:] == ["conv"]:
+        gen_conv("conv_64x64_5x5", (64, 64), (5, 5))
+        gen_conv("conv_4x4_5x5_stress", (4, 4), (5, 5))
+        sys.exit(0)
     gen_scheme("bfv8k", bfv8k, BfvCiphertextNode, BfvPlaintextNode, BfvPlaintextRingtNode, BfvPlaintextMulNode, 2, 1)
     gen_scheme("ckks8k", ckks8k, CkksCiphertextNode, CkksPlaintextNode, CkksPlaintextRingtNode, CkksPlaintextMulNode, 4, 1)
     gen_ckks_extra("ckks8k", ckks8k, 4)

@@ -83,8 +83,10 @@ def _mulmod_rows(x, y, q):
 class GraphCase:
     """One task directory: random inputs (seeded), oracle evaluation, run through the runner."""
 
-    def __init__(self, path, seed=7):
+    def __init__(self, path, seed=7, pt_pool=0):
+        """pt_pool > 0: plaintext inputs of one level share pt_pool distinct random arrays (large graphs)."""
         self.path = path
+        self.pt_pool = pt_pool
         with open(os.path.join(path, "mega_ag.json")) as f:
             self.g = json.load(f)
         with open(os.path.join(path, "task_signature.json")) as f:
@@ -109,13 +111,20 @@ class GraphCase:
     def _make_inputs(self, seed):
         q, p = self.params.q, self.params.p
         self.glk = {}
+        self._pool = {}
         for idx in self.g["inputs"]:
             d = self.data[idx]
             t, lv = d["type"], d["level"]
             if t in ("ct", "ct3"):
                 self.values[idx] = self._rand_limbs((d["degree"] + 1,), q[:lv + 1])
             elif t in ("pt", "pt_mul"):
-                self.values[idx] = self._rand_limbs((), q[:lv + 1])
+                if self.pt_pool:
+                    key = (lv, idx % self.pt_pool)
+                    if key not in self._pool:
+                        self._pool[key] = self._rand_limbs((), q[:lv + 1])
+                    self.values[idx] = self._pool[key]
+                else:
+                    self.values[idx] = self._rand_limbs((), q[:lv + 1])
             elif t == "pt_ringt":
                 tt = self.params.t if self.params.scheme == R.SCHEME_BFV else 65537
                 self.values[idx] = self.rng.integers(0, tt, size=(1, self.N), dtype=np.uint64)
@@ -209,8 +218,14 @@ class GraphCase:
             raise ValueError("unknown custom node " + t)
         raise ValueError("unsupported node type " + t)
 
-    def expected(self):
+    def expected(self, free=False):
+        """free=True drops an intermediate once its last consumer has run (large graphs)."""
         pending = dict(self.compute)
+        uses = {}
+        for c in self.compute.values():
+            for i in c["inputs"]:
+                uses[i] = uses.get(i, 0) + 1
+        keep = set(self.g["inputs"]) | set(self.g["outputs"])
         while pending:
             progressed = False
             for k in sorted(pending):
@@ -219,6 +234,11 @@ class GraphCase:
                     self.values[c["outputs"][0]] = self._eval_node(c)
                     del pending[k]
                     progressed = True
+                    if free:
+                        for i in c["inputs"]:
+                            uses[i] -= 1
+                            if uses[i] == 0 and i not in keep:
+                                del self.values[i]
             if not progressed:
                 raise RuntimeError("graph evaluation stuck")
         return [self.values[i] for i in self.g["outputs"]]
@@ -324,4 +344,23 @@ class GraphCase:
 
 
 def all_cases():
-    return sorted(d for d in os.listdir(GRAPHS) if os.path.isdir(os.path.join(GRAPHS, d)))
+    return sorted(d for d in os.listdir(GRAPHS) if os.path.exists(os.path.join(GRAPHS, d, "mega_ag.json")))
+
+
+def unpack_case(case, dest):
+    """Large fixtures are committed gzipped (tests/golden/graphs/<case>/*.json.gz); the runner wants plain files."""
+    import gzip
+    import shutil
+    os.makedirs(dest, exist_ok=True)
+    for f in ("mega_ag.json", "task_signature.json"):
+        with gzip.open(os.path.join(GRAPHS, case, f + ".gz"), "rb") as src, open(os.path.join(dest, f), "wb") as dst:
+            shutil.copyfileobj(src, dst)
+    return dest
+
+
+def digest(arrays):
+    import hashlib
+    h = hashlib.sha256()
+    for a in arrays:
+        h.update(np.ascontiguousarray(a, dtype=np.uint64).tobytes())
+    return h.hexdigest()

@@ -202,6 +202,47 @@ void launch_mul_plain(const DeviceTables& dt, BatchPtr ct, BatchPtr pt, BatchPtr
     LSB_CUDA(cudaGetLastError());
 }
 
+// ---- n-ary sum: out = sum_t ct_t * pt_t + sum_u ct_u  (one pass over every term) --------------------
+// The runner re-associates chains of ciphertext additions (and the ct x pt products feeding them) into one of
+// these: modular addition is associative, so the limbs equal those of the node-by-node evaluation.
+struct SumTermsArgs {
+    const u64* const* ct;  // [n_mac + n_plain][batch]
+    const u64* const* pt;  // [n_mac][batch]
+    u64* const* out;       // [batch]
+    int N, nl, n_mac, n_plain, batch;
+    const ModConst* mods;
+};
+__global__ void __launch_bounds__(kElemThreads) k_sum_terms(const __grid_constant__ SumTermsArgs g) {
+    const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j2 >= g.N / 2) return;
+    const int r = blockIdx.y, b = blockIdx.z, i = r % g.nl;
+    const BarrettQ bq = g.mods[i].bq;
+    const size_t coff = (size_t)r * g.N, poff = (size_t)i * g.N;
+    W2 acc{0, 0};
+#pragma unroll 4
+    for (int t = 0; t < g.n_mac; t++) {
+        const W2 c = ld2(g.ct[(size_t)t * g.batch + b] + coff, j2);
+        const W2 p = ld2(g.pt[(size_t)t * g.batch + b] + poff, j2);
+        acc.a = addmod(acc.a, mulmod(c.a, p.a, bq), bq.q);
+        acc.b = addmod(acc.b, mulmod(c.b, p.b, bq), bq.q);
+    }
+#pragma unroll 4
+    for (int t = 0; t < g.n_plain; t++) {
+        const W2 c = ld2(g.ct[(size_t)(g.n_mac + t) * g.batch + b] + coff, j2);
+        acc.a = addmod(acc.a, c.a, bq.q);
+        acc.b = addmod(acc.b, c.b, bq.q);
+    }
+    st2(g.out[b] + coff, j2, acc);
+}
+void launch_sum_terms(const DeviceTables& dt, const u64* const* ct, const u64* const* pt, u64* const* out, int npoly, int nl,
+                      int n_mac, int n_plain, int batch, cudaStream_t s) {
+    if (batch <= 0) return;
+    SumTermsArgs g{ct, pt, out, dt.N, nl, n_mac, n_plain, batch, dt.mods};
+    ProfScope _ps(dt.prof, PK_ELEMWISE, s, 8.0 * dt.N * nl * batch * (npoly * (n_mac + n_plain + 1.0) + n_mac));
+    k_sum_terms<<<elem_grid(dt.N, npoly * nl, batch), kElemThreads, 0, s>>>(g);
+    LSB_CUDA(cudaGetLastError());
+}
+
 // ---- basis extension -----------------------------------------------------------------------------
 struct BexArgs {
     const BexJob* jobs;

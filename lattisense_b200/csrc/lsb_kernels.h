@@ -83,6 +83,8 @@ void launch_negate(const DeviceTables& dt, BatchPtr a, BatchPtr out, const RowMa
 void launch_tensor(const DeviceTables& dt, BatchPtr a, BatchPtr b, BatchPtr out, int nl, int a_poly_stride,
                    int out_poly_stride, const uint8_t* mod_of_limb, int batch, cudaStream_t s);
 // out[p][i] (+)= ct[p][i] * pt[i]  (NTT domain), p < npoly
+void launch_sum_terms(const DeviceTables& dt, const u64* const* ct, const u64* const* pt, u64* const* out, int npoly, int nl,
+                      int n_mac, int n_plain, int batch, cudaStream_t s);
 void launch_mul_plain(const DeviceTables& dt, BatchPtr ct, BatchPtr pt, BatchPtr out, int npoly, int nl,
                       bool accumulate, int batch, cudaStream_t s);
 // out[r] = (a[a_slot[r]] - b[b_slot[r]]) * c_r (+ addend[add_slot[r]])   (ModDown / rescale finish)

@@ -502,6 +502,16 @@ void op_mac(OpEnv& e, int level, int nterms, const BatchPtr* cts, const BatchPtr
     }
 }
 
+// out_b = sum_{t<n_mac} ct[t][b] * pt[t][b] + sum_{u<n_plain} ct[n_mac+u][b]   (tables are device arrays [term][batch]).
+// Products need NTT-domain operands, i.e. CKKS ciphertexts and plaintexts; plain terms are limb-wise in any domain.
+void op_sum_terms(OpEnv& e, int level, int npoly, const u64* const* ct_tab, const u64* const* pt_tab, u64* const* out_tab,
+                  int n_mac, int n_plain, int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    LSB_CHECK(level >= 0 && level < e.c.nq && npoly >= 1 && n_mac >= 0 && n_plain >= 0 && n_mac + n_plain >= 1, "lsb: sum_terms: bad arguments");
+    LSB_CHECK(n_mac == 0 || e.c.scheme == SCHEME_CKKS, "lsb: sum_terms: fused products need NTT-domain (CKKS) operands");
+    launch_sum_terms(e.c.dt, ct_tab, pt_tab, out_tab, npoly, level + 1, n_mac, n_plain, batch, e.s);
+}
+
 // ---------------------------------------------------------------------------------------------
 // fused chains
 // ---------------------------------------------------------------------------------------------

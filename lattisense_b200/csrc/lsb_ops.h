@@ -41,6 +41,8 @@ void op_mul_plain_ringt(OpEnv& e, int level, int npoly, BatchPtr ct, BatchPtr pt
 
 // bind_gpu_cmp_sum / bind_gpu_cmpac_sum (:294-408): sum_i ct_i x pt_i (+ acc_in); pts are pt_ringt ([1][N] mod t)
 // when `ringt`, NTT-domain [level+1][N] plaintexts otherwise
+void op_sum_terms(OpEnv& e, int level, int npoly, const u64* const* ct_tab, const u64* const* pt_tab, u64* const* out_tab,
+                  int n_mac, int n_plain, int batch);
 void op_mac(OpEnv& e, int level, int nterms, const BatchPtr* cts, const BatchPtr* pts, bool ringt, bool has_acc,
             BatchPtr acc_in, BatchPtr out, int batch);
 

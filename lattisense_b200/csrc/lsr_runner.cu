@@ -333,6 +333,8 @@ struct Unit {
     int slot = 0;                          // device slot; -1: every device (key load)
     int component = -1;
     int order_key = 0;                     // LOAD: id of the first GPU unit that consumes the object (-1: key)
+    // re-associated sum (nodes = absorbed products, inner additions, root addition last): out = sum ct [* pt]
+    std::vector<std::pair<DatumNode*, DatumNode*>> sum_terms;  // (ciphertext, plaintext or nullptr)
 };
 
 struct Plan {
@@ -391,6 +393,64 @@ static Plan build_plan(TaskGraph& g, bool fuse, bool fuse_host) {
             chains[m] = chain;
         }
     }
+    // pass 1a': sums.  A tree of ct + ct additions whose inner results have no other reader becomes ONE n-ary sum, and a
+    // CKKS ct x pt product read only by that sum becomes a multiply-accumulate term of it.  The packed convolution of
+    // examples/benchmark_convolution accumulates 12 800 products through a chain of 12 800 dependent additions
+    // (benchmark_convolution.py:143-156): node by node that is 12 800 scheduling waves, re-associated it is one pass over
+    // the terms.  Modular addition is associative and commutative, so every limb is unchanged.
+    std::unordered_map<ComputeNode*, std::vector<std::pair<DatumNode*, DatumNode*>>> sums;
+    if (fuse) {
+        auto is_ct = [](const DatumNode* d) { return d->fhe_prop.has_value() && d->datum_type == TYPE_CIPHERTEXT; };
+        auto is_sum_add = [&](const ComputeNode* c) {
+            if (!is_device_op(c) || op_of(c) != OperationType::ADD || c->input_nodes.size() != 2 || c->output_nodes.size() != 1) return false;
+            const DatumNode *a = c->input_nodes[0], *b = c->input_nodes[1], *o = c->output_nodes[0];
+            return is_ct(a) && is_ct(b) && is_ct(o) && a->fhe_prop->level == b->fhe_prop->level && a->fhe_prop->degree == b->fhe_prop->degree &&
+                   o->fhe_prop->level == a->fhe_prop->level && o->fhe_prop->degree == a->fhe_prop->degree;
+        };
+        auto pure_single = [](const DatumNode* d) { return !d->is_output && !d->is_input && d->successors.size() == 1 && d->predecessors.size() == 1; };
+        for (NodeIndex ci : order) {
+            ComputeNode* root = &g.computes.at(ci);
+            if (!is_sum_add(root) || absorbed.count(root)) continue;
+            const DatumNode* ro = root->output_nodes[0];
+            if (pure_single(ro) && is_sum_add(ro->successors[0])) continue;  // an inner node of somebody else's sum
+            std::vector<ComputeNode*> inner, prods;
+            std::vector<std::pair<DatumNode*, DatumNode*>> mac, plain;
+            std::vector<DatumNode*> stack{root->input_nodes[1], root->input_nodes[0]};
+            while (!stack.empty()) {
+                DatumNode* d = stack.back();
+                stack.pop_back();
+                ComputeNode* pn = pure_single(d) ? d->predecessors[0] : nullptr;
+                if (pn && !absorbed.count(pn) && is_sum_add(pn)) {
+                    inner.push_back(pn);
+                    stack.push_back(pn->input_nodes[1]);
+                    stack.push_back(pn->input_nodes[0]);
+                    continue;
+                }
+                if (pn && !absorbed.count(pn) && !chains.count(pn) && g.algo == ALGO_CKKS && is_device_op(pn) && op_of(pn) == OperationType::MULTIPLY &&
+                    pn->input_nodes.size() == 2 && pn->output_nodes.size() == 1) {
+                    DatumNode *x = pn->input_nodes[0], *y = pn->input_nodes[1];
+                    if (!is_ct(x)) std::swap(x, y);
+                    const bool plain_pt = y->fhe_prop.has_value() && y->datum_type == TYPE_PLAINTEXT &&
+                                          !(y->fhe_prop->p.has_value() && y->fhe_prop->p->is_ringt);
+                    if (is_ct(x) && plain_pt && x->fhe_prop->level == d->fhe_prop->level && x->fhe_prop->degree == d->fhe_prop->degree &&
+                        y->fhe_prop->level == d->fhe_prop->level) {
+                        prods.push_back(pn);
+                        mac.emplace_back(x, y);
+                        continue;
+                    }
+                }
+                plain.emplace_back(d, nullptr);
+            }
+            if (inner.size() + prods.size() == 0) continue;  // a lone addition of two finished ciphertexts
+            std::vector<ComputeNode*> nodes = prods;
+            nodes.insert(nodes.end(), inner.rbegin(), inner.rend());
+            nodes.push_back(root);
+            for (size_t i = 0; i + 1 < nodes.size(); i++) absorbed.insert(nodes[i]);
+            chains[root] = nodes;
+            mac.insert(mac.end(), plain.begin(), plain.end());
+            sums[root] = std::move(mac);
+        }
+    }
     // pass 1b: host chains.  EXPORT_TO_ABI -> LOAD_TO_BACKEND and STORE_FROM_BACKEND -> IMPORT_FROM_ABI run back to
     // back on one worker thread: the limbs EXPORT just wrote are still in that core's cache when LOAD stages them,
     // and IMPORT reads the stored object straight out of the pinned staging region (no intermediate copy).
@@ -419,6 +479,8 @@ static Plan build_plan(TaskGraph& g, bool fuse, bool fuse_host) {
         if (it != chains.end()) {
             u.nodes = it->second;
             if (is_device_op(c)) p.fused_nodes += (long long)u.nodes.size() - 1;
+            auto st = sums.find(c);
+            if (st != sums.end()) u.sum_terms = st->second;
         } else {
             u.nodes = {c};
         }
@@ -905,7 +967,7 @@ void RunState::start_store_unit(const Unit& u) {
 // ---------------------------------------------------------------------------------------------
 enum CallKind {
     K_ADD_CC, K_SUB_CC, K_ADD_CP, K_ADD_CPR, K_SUB_PC, K_SUB_PRC, K_NEG, K_MULT_CC, K_MUL_CP, K_MUL_CPR, K_RELIN, K_RESCALE,
-    K_DROP, K_ROTATE, K_MAC, K_MULT_RELIN, K_MULT_RELIN_RESCALE
+    K_DROP, K_ROTATE, K_MAC, K_MULT_RELIN, K_MULT_RELIN_RESCALE, K_SUM
 };
 struct GpuCall {
     int kind = 0, level = 0, npoly = 2, aux = 0, aux2 = 0;  // aux: subtract flag / ringt flag / sum_cnt ; aux2: has partial sum
@@ -958,6 +1020,16 @@ GpuCall RunState::describe(const Unit& u, const std::unordered_map<NodeIndex, st
     LSB_CHECK(out->fhe_prop.has_value(), "mega_ag: output of '" + n0.id + "' has no FHE properties");
     c.out_level = out->fhe_prop->level;
     c.out_npoly = out->fhe_prop->degree + 1;
+    if (!u.sum_terms.empty()) {  // re-associated sum: operands = ciphertexts (product terms first), then their plaintexts
+        c.kind = K_SUM;
+        c.level = c.out_level;
+        c.npoly = c.out_npoly;
+        for (auto& t : u.sum_terms) c.aux += t.second ? 1 : 0;
+        for (auto& t : u.sum_terms) c.operands.push_back(dev(t.first));
+        for (auto& t : u.sum_terms)
+            if (t.second) c.operands.push_back(dev(t.second));
+        return c;
+    }
     if (u.nodes.size() > 1) {  // fused mult -> relin [-> rescale]
         need(1);
         const ComputeNode& relin = *u.nodes[1];
@@ -1137,6 +1209,32 @@ void RunState::exec_group(int slot, const std::vector<int>& members, const GpuCa
         optr[i] = outs[i]->ptr;
     }
     const size_t nops = rep.operands.size();
+    if (rep.kind == K_SUM) {
+        // one pointer table [operand][batch] per sub-batch instead of one table per operand: a sum can have 10^4 terms
+        lsb::OpEnv e{ctx, *rt->ws, rt->compute, 0};
+        const int n_mac = rep.aux, n_terms = (int)nops - n_mac;
+        LSB_CHECK(nops + 1 <= rt->tab_cap / 2, "lsb runner: sum has too many terms for the pointer-table arena");
+        const int step = (int)std::max<size_t>(1, std::min<size_t>((size_t)nb, rt->tab_cap / 2 / (nops + 1)));
+        for (int b0 = 0; b0 < nb; b0 += step) {
+            const int cb = std::min(step, nb - b0);
+            std::vector<u64*> ptrs((nops + 1) * (size_t)cb);
+            for (size_t j = 0; j < nops; j++)
+                for (int i = 0; i < cb; i++) ptrs[j * cb + i] = calls[b0 + i].operands[j]->ptr;
+            for (int i = 0; i < cb; i++) ptrs[nops * cb + i] = optr[b0 + i];
+            u64** tab = push_table(rt, ptrs);
+            lsb::op_sum_terms(e, rep.level, rep.npoly, tab, tab + (size_t)n_terms * cb, tab + nops * cb, n_mac, n_terms - n_mac, cb);
+        }
+        groups++;
+        for (int i = 0; i < nb; i++) {
+            DatumPtr d = std::make_shared<DeviceDatum>();
+            d->on.resize(slots.size());
+            d->on[slot] = outs[i];
+            calls[i].operands.clear();
+            calls[i].keepalive.clear();
+            unit_done(plan.units[members[i]], d, false);
+        }
+        return;
+    }
     std::vector<BatchPtr> tabs(nops);
     for (size_t j = 0; j < nops; j++) {
         std::vector<u64*> ptrs(nb);

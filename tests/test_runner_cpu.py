@@ -120,3 +120,38 @@ def test_run_without_gpu_fails_loudly():
     case = GE.GraphCase(os.path.join(GE.GRAPHS, "ckks8k_cac"))
     with pytest.raises(RuntimeError, match="no CUDA device|CUDA|cuda"):
         case.run()
+
+
+def test_sum_reassociation_in_the_plan(tmp_path, monkeypatch):
+    # packed convolution, 64x64 input / 5x5 kernel: 50 ct x pt products accumulated through 49 dependent additions
+    # (+ rescale + bias): the products and the additions collapse into ONE n-ary multiply-accumulate unit
+    h, t, d = _describe("conv_64x64_5x5")
+    try:
+        assert d["gpu"] == 49 + 1 + 1 + 1          # rotations, the sum, rescale, + bias
+        assert d["fused"] == 50 + 49 - 1
+    finally:
+        h.th_close(t)
+    monkeypatch.setenv("LSB_NO_FUSE", "1")
+    h, t, d = _describe("conv_64x64_5x5")
+    try:
+        assert (d["gpu"], d["fused"]) == (150, 0)
+    finally:
+        h.th_close(t)
+    monkeypatch.delenv("LSB_NO_FUSE")
+    # BFV degree-7 polynomial: products of ct x pt_mul are not folded (they need their own NTT round trip), the six
+    # additions between them are one sum
+    h, t, d = _describe("cfg3_bfv_poly7")
+    try:
+        assert d["fused"] >= 5
+    finally:
+        h.th_close(t)
+    # the 38 400-node stress graph: 12 799 rotations + 1 sum + rescale + bias
+    h = GE.harness()
+    t = h.th_open(GE.unpack_case("conv_4x4_5x5_stress", str(tmp_path)).encode(), 1)
+    assert t, h.th_last_error().decode()
+    try:
+        out = (C.c_longlong * 8)()
+        assert GE.runner_lib().lsb_gpu_task_describe(t, out) == 0
+        assert out[5] == 12799 + 3 and out[6] == 12800 + 12799 - 1
+    finally:
+        h.th_close(t)

@@ -241,8 +241,24 @@ def gen_logreg_n65536():
          [Argument("out", o)])
 
 
+def gen_seal_flavoured():
+    """Rotations as the SEAL plug-in's frontend emits them (custom_task.py:1586-1740): Galois generator 3 instead of 5, the
+    element carried by the key datum - the runner must take it from there, not from the step."""
+    for tag, mkparam, Ct, lv in (("bfv8k", bfv8k, BfvCiphertextNode, 2), ("ckks8k", ckks8k, CkksCiphertextNode, 4)):
+        set_fhe_param(mkparam())
+        xs = [Ct(f"x_{i}", level=lv) for i in range(N_OP)]
+        ys = [seal_rotate_cols(xs[i], [1, 6, -3]) for i in range(N_OP)]
+        zs = [seal_rotate_rows(xs[i], f"z_{i}") for i in range(N_OP)]
+        ws = [seal_advanced_rotate_cols(xs[i], [20, -500]) for i in range(N_OP)]
+        emit(f"{tag}_seal_rotate", [Argument("in_x_list", xs)],
+             [Argument("out_y_list", ys), Argument("out_z_list", zs), Argument("out_w_list", ws)])
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if sys.argv[1:] == ["seal"]:
+        gen_seal_flavoured()
+        sys.exit(0)
     if sys.argv[1:] == ["n65536"]:
         gen_logreg_n65536()
         sys.exit(0)

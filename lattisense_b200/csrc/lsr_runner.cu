@@ -368,6 +368,13 @@ static ComputeNode* sole_consumer(const DatumNode* d, OperationType want) {
     return c->input_nodes[0] == d ? c : nullptr;
 }
 
+// Keys and plaintexts are read-only inputs that several otherwise independent sub-graphs may share (cfg3 x B: one set of
+// polynomial coefficients for every evaluation): they do not join DAG components, each is loaded onto every device
+// that runs one of its consumers.
+static bool replicated_datum(const DatumNode* d) {
+    return d->fhe_prop.has_value() && (is_key_type(d->datum_type) || d->datum_type == TYPE_PLAINTEXT);
+}
+
 static Plan build_plan(TaskGraph& g, bool fuse, bool fuse_host) {
     Plan p;
     p.total_nodes = g.computes.size();
@@ -516,7 +523,7 @@ static Plan build_plan(TaskGraph& g, bool fuse, bool fuse_host) {
         if (!key && it != p.consumers.end())
             for (int v : it->second) u.order_key = std::min(u.order_key, v);
     }
-    // components: units joined through non-key data (keys are shared by everything and replicated instead)
+    // components: units joined through ciphertext data (keys and plaintexts are replicated instead)
     std::vector<int> parent(p.units.size());
     for (size_t i = 0; i < parent.size(); i++) parent[i] = (int)i;
     std::function<int(int)> find = [&](int x) {
@@ -524,14 +531,14 @@ static Plan build_plan(TaskGraph& g, bool fuse, bool fuse_host) {
         return x;
     };
     for (Unit& u : p.units) {
-        if (u.output->fhe_prop.has_value() && is_key_type(u.output->datum_type)) continue;
+        if (replicated_datum(u.output)) continue;
         auto it = p.consumers.find(u.output->index);
         if (it == p.consumers.end()) continue;
         for (int v : it->second) parent[find(v)] = find(u.id);
     }
     std::unordered_map<int, int> comp_id;
     for (Unit& u : p.units) {
-        const bool key_chain = u.output->fhe_prop.has_value() && is_key_type(u.output->datum_type);
+        const bool key_chain = replicated_datum(u.output);
         if (key_chain) {
             u.component = -1;
             u.slot = -1;
@@ -830,9 +837,20 @@ void RunState::run_load_unit(const Unit& u) {
         DatumPtr datum = std::make_shared<DeviceDatum>();
         datum->on.resize(slots.size());
         const int my_slot = slot_of(u);
+        // a replicated object (key, plaintext) goes to every device that runs one of its consumers
+        std::vector<char> wanted(slots.size(), my_slot < 0 ? 0 : 1);
+        if (my_slot < 0) {
+            auto cons = plan.consumers.find(u.output->index);
+            if (cons != plan.consumers.end())
+                for (int v : cons->second) {
+                    const int cs = slot_of(plan.units[v]);
+                    if (cs >= 0) wanted[cs] = 1;
+                    else std::fill(wanted.begin(), wanted.end(), 1);
+                }
+        }
         bool first = true;
         for (int s = 0; s < (int)slots.size(); s++) {
-            if (my_slot >= 0 && s != my_slot) continue;
+            if (!wanted[s] || (my_slot >= 0 && s != my_slot)) continue;
             DeviceRuntime* rt = slots[s];
             LSB_CUDA(cudaSetDevice(rt->device));
             uint64_t ticket = 0;

@@ -254,8 +254,38 @@ def gen_seal_flavoured():
              [Argument("out_y_list", ys), Argument("out_z_list", zs), Argument("out_w_list", ws)])
 
 
+def gen_cfg3_replicas(copies=8):
+    """cfg3 as BASELINE.json shards it over 2/4/8 GPUs: `copies` independent degree-7 polynomial evaluations (one DAG
+    component each; a single instance has a critical path of 3 mult_relin and cannot use several GPUs), shared rlk."""
+    set_fhe_param(BfvParam.create_default_param(n=16384))
+    level = 4
+    a = [BfvPlaintextMulNode(f"a_{i}", level - 3) for i in range(1, 8)]
+    a0 = BfvPlaintextNode("a_0", level - 3)
+    xs, ys = [], []
+    for b in range(copies):
+        x = BfvCiphertextNode(f"x_{b}", level)
+        x2 = rescale(mult_relin(x, x))
+        x3 = rescale(mult_relin(x2, rescale(x)))
+        x4 = rescale(mult_relin(x2, x2))
+        x5 = rescale(mult_relin(x3, rescale(x2)))
+        x6 = rescale(mult_relin(x3, x3))
+        x7 = rescale(mult_relin(x3, x4))
+        pw = [rescale(rescale(rescale(x))), rescale(rescale(x2)), rescale(x3), rescale(x4), x5, x6, x7]
+        acc = None
+        for i in range(7):
+            term = mult(pw[i], a[i])
+            acc = term if acc is None else add(acc, term)
+        xs.append(x)
+        ys.append(add(acc, a0, f"y_{b}"))
+    emit(f"cfg3_bfv_poly7_x{copies}", [Argument("x", xs), Argument("a", a), Argument("a_0", a0)], [Argument("y", ys)])
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if sys.argv[1:] == ["cfg3x"]:
+        gen_cfg3_replicas(8)
+        gen_cfg3_replicas(64)  # throughput fixture for tools/multi_device_run.py; gzip it after generation
+        sys.exit(0)
     if sys.argv[1:] == ["seal"]:
         gen_seal_flavoured()
         sys.exit(0)

@@ -8,6 +8,7 @@
 //    write per limb (16*N bytes, the algorithmic minimum), persistent grid-stride loop over rows.
 //  * N  = 2^15, 2^16: column pass (stages [0, logN-8) on 16-column strided tiles, 128-byte
 //    segments) + row pass (last 8 stages on 4096-word contiguous tiles).
+#include <atomic>
 #include <type_traits>
 #include <cstdlib>
 #include "lsb_kernels.h"
@@ -194,14 +195,23 @@ __global__ void __launch_bounds__(256) k_ntt_rows(const __grid_constant__ NttArg
     }
 }
 
+constexpr int kMaxDevices = 64;
+static int current_device() {
+    int dev = 0;
+    LSB_CUDA(cudaGetDevice(&dev));
+    LSB_CHECK(dev >= 0 && dev < kMaxDevices, "lsb: device ordinal out of range");
+    return dev;
+}
+
 // ---------------------------------------------------------------------------------------------
 template <int LOGN, bool INV>
 static void launch_single(const NttArgs& a, int sms, cudaStream_t s) {
     constexpr int smem = (1 << LOGN) * 8;
-    static bool attr_done = false;
-    if (!attr_done) {
+    static std::atomic<bool> attr_done[kMaxDevices];  // function attributes are per device
+    const int dev = current_device();
+    if (!attr_done[dev].load(std::memory_order_acquire)) {
         LSB_CUDA(cudaFuncSetAttribute(k_ntt_single<LOGN, INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        attr_done = true;
+        attr_done[dev].store(true, std::memory_order_release);
     }
     int per_sm = (200 * 1024) / smem;
     if (per_sm < 1) per_sm = 1;
@@ -215,11 +225,12 @@ static void launch_two_pass(NttArgs a, int sms, cudaStream_t s) {
     constexpr int LA = LOGN - kRowLS;
     constexpr int smem_c = (1 << (LA + kColLC)) * 8, nt_c = (1 << (LA + kColLC)) / 16;
     constexpr int smem_r = (1 << kRowLS) * kRowSub * 8;
-    static bool attr_done = false;
-    if (!attr_done) {
+    static std::atomic<bool> attr_done[kMaxDevices];  // function attributes are per device
+    const int dev = current_device();
+    if (!attr_done[dev].load(std::memory_order_acquire)) {
         LSB_CUDA(cudaFuncSetAttribute(k_ntt_cols<LOGN, INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_c));
         LSB_CUDA(cudaFuncSetAttribute(k_ntt_rows<LOGN, INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_r));
-        attr_done = true;
+        attr_done[dev].store(true, std::memory_order_release);
     }
     const int units_c = a.total_rows * ((1 << kRowLS) >> kColLC);
     const int units_r = a.total_rows * ((1 << LOGN) / ((1 << kRowLS) * kRowSub));

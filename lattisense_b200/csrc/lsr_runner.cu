@@ -630,19 +630,25 @@ struct RunState {
     std::unordered_map<NodeIndex, void*> output_handles;
     std::vector<int> remaining;
     std::unordered_map<NodeIndex, int> refcnt;
-    std::vector<int> ready;
+    std::vector<std::vector<int>> ready_q;  // one queue per device slot; units without a device (host nodes, replicated loads) use queue 0
+    bool aborted = false;                    // a dispatcher died: everybody leaves
     size_t done_units = 0;
     int in_flight = 0;  // units handed to the worker pool and not finished
+    int feeding = 0;    // ... of which can still make GPU units ready (loads, host nodes; not the result drains)
     std::atomic<size_t> completed_nodes{0};
     std::atomic<bool> failed{false};
     std::string error;
     std::atomic<int64_t> last_progress_ns{0};
-    long long groups = 0;
+    std::atomic<long long> groups{0};
 
     RunState(GpuTask& t, WorkerPool& wp, progress_callback_t cb, void* ud)
         : task(t), g(*t.graph), plan(t.plan), pool(wp), progress_cb(cb), user_data(ud) {}
 
     int slot_of(const Unit& u) const { return u.component >= 0 ? slot_of_component[u.component] : -1; }
+    static bool feeds_gpu(const Unit& u) {
+        return u.kind == UnitKind::LOAD || (u.kind == UnitKind::HOST && op_of(u.nodes[0]) != OperationType::IMPORT_FROM_ABI);
+    }
+    int queue_of(int unit) const { return std::max(0, slot_of(plan.units[unit])); }
 
     void fail(const std::string& what) {
         std::lock_guard<std::mutex> lk(mu);
@@ -681,9 +687,12 @@ struct RunState {
             auto c = plan.consumers.find(u.output->index);
             if (c != plan.consumers.end())
                 for (int v : c->second)
-                    if (--remaining[v] == 0) ready.push_back(v);
+                    if (--remaining[v] == 0) ready_q[queue_of(v)].push_back(v);
             done_units++;
-            if (from_pool) in_flight--;
+            if (from_pool) {
+                in_flight--;
+                if (feeds_gpu(u)) feeding--;
+            }
         }
         cv.notify_all();
         const size_t done = completed_nodes.fetch_add(u.nodes.size()) + u.nodes.size();
@@ -707,7 +716,7 @@ struct RunState {
     void flush_gpu(std::vector<int>& pending);
     void exec_group(int slot, const std::vector<int>& members, const struct GpuCall& rep, std::vector<struct GpuCall>& calls);
     struct GpuCall describe(const Unit& u, const std::unordered_map<NodeIndex, std::any>& in, int slot);
-    void dispatch();
+    void dispatch(int q);
 };
 
 // worker-pool priorities: results drain first, then input staging in consumer order, then other host nodes
@@ -1329,27 +1338,32 @@ void RunState::flush_gpu(std::vector<int>& pending) {
         }
     }
     pending.clear();
-    for (const std::string& sig : order) {
-        auto& grp = groups_by_sig.at(sig);
-        const int slot = slot_of(plan.units[grp.first[0]]);
-        try {
-            if (failed.load()) throw std::runtime_error("cancelled");
-            GpuCall rep = grp.second[0];
-            exec_group(slot, grp.first, rep, grp.second);
-        } catch (const std::exception& e) {
-            if (std::string(e.what()) != "cancelled") fail(std::string("GPU batch (") + plan.units[grp.first[0]].nodes[0]->id + ", " +
-                                                           std::to_string(grp.first.size()) + " nodes): " + e.what());
-            // publish empty outputs so that the graph drains
-            for (int ui : grp.first) {
-                bool already;
-                {
-                    std::lock_guard<std::mutex> lk(mu);
-                    already = avail.count(plan.units[ui].output->index) != 0;
+    auto run_sigs = [&](const std::vector<const std::string*>& sigs) {
+        for (const std::string* sp : sigs) {
+            auto& grp = groups_by_sig.at(*sp);
+            const int slot = slot_of(plan.units[grp.first[0]]);
+            try {
+                if (failed.load()) throw std::runtime_error("cancelled");
+                GpuCall rep = grp.second[0];
+                exec_group(slot, grp.first, rep, grp.second);
+            } catch (const std::exception& e) {
+                if (std::string(e.what()) != "cancelled") fail(std::string("GPU batch (") + plan.units[grp.first[0]].nodes[0]->id + ", " +
+                                                               std::to_string(grp.first.size()) + " nodes): " + e.what());
+                // publish empty outputs so that the graph drains
+                for (int ui : grp.first) {
+                    bool already;
+                    {
+                        std::lock_guard<std::mutex> lk(mu);
+                        already = avail.count(plan.units[ui].output->index) != 0;
+                    }
+                    if (!already) unit_done(plan.units[ui], std::any(), false);
                 }
-                if (!already) unit_done(plan.units[ui], std::any(), false);
             }
         }
-    }
+    };
+    std::vector<const std::string*> all;
+    for (const std::string& sig : order) all.push_back(&sig);
+    run_sigs(all);
 }
 
 
@@ -1357,11 +1371,14 @@ void RunState::flush_gpu(std::vector<int>& pending) {
 // dispatcher (runs on the caller's thread; replaces run_tasks, cpu_task_utils.h:377-569, and the
 // submit_gpu_task lambda of gpu_wrapper.cu:204-352)
 // ---------------------------------------------------------------------------------------------
-void RunState::dispatch() {
+void RunState::dispatch(int q) {
+    std::vector<int>& ready = ready_q[q];
     const size_t total_units = plan.units.size();
     const size_t batch_min = env_mb("LSB_BATCH_MIN", 128);
     const auto linger = std::chrono::microseconds(env_mb("LSB_BATCH_LINGER_US", 1000));
     std::vector<int> gpu_pending;
+    const bool trace = getenv("LSB_TRACE") != nullptr;  // dispatcher timeline on stderr
+    const auto t_start = std::chrono::steady_clock::now();
     auto pending_since = std::chrono::steady_clock::now();
     for (;;) {
         std::vector<int> batch;
@@ -1369,15 +1386,15 @@ void RunState::dispatch() {
         {
             std::unique_lock<std::mutex> lk(mu);
             if (ready.empty() && gpu_pending.empty()) {
-                if (done_units >= total_units) break;
-                cv.wait(lk, [&] { return !ready.empty() || done_units >= total_units; });
+                if (done_units >= total_units || aborted) break;
+                cv.wait(lk, [&] { return !ready.empty() || done_units >= total_units || aborted; });
                 if (ready.empty()) break;
             } else if (ready.empty()) {
                 // GPU work is waiting to be batched: give in-flight host nodes a moment to add to it
-                if (in_flight > 0 && gpu_pending.size() < batch_min) cv.wait_until(lk, pending_since + linger, [&] { return !ready.empty(); });
+                if (feeding > 0 && gpu_pending.size() < batch_min) cv.wait_until(lk, pending_since + linger, [&] { return !ready.empty(); });
             }
             batch.swap(ready);
-            flying = in_flight;
+            flying = feeding;
         }
         std::stable_sort(batch.begin(), batch.end(), [&](int a, int b) { return plan.units[a].priority > plan.units[b].priority; });
         for (int ui : batch) {
@@ -1388,6 +1405,7 @@ void RunState::dispatch() {
                     {
                         std::lock_guard<std::mutex> lk(mu);
                         in_flight++;
+                        if (feeds_gpu(u)) feeding++;
                     }
                     const Unit* up = &u;
                     if (u.kind == UnitKind::HOST) {
@@ -1410,12 +1428,25 @@ void RunState::dispatch() {
             {
                 std::lock_guard<std::mutex> lk(mu);
                 more_ready = !ready.empty();
-                flying = in_flight;
+                flying = feeding;
             }
             const bool waited = std::chrono::steady_clock::now() - pending_since >= linger;
-            if (gpu_pending.size() >= batch_min || (!more_ready && (flying == 0 || waited))) flush_gpu(gpu_pending);
+            if (gpu_pending.size() >= batch_min || (!more_ready && (flying == 0 || waited))) {
+                const auto f0 = std::chrono::steady_clock::now();
+                const size_t np = gpu_pending.size();
+                flush_gpu(gpu_pending);
+                if (trace) {
+                    const auto f1 = std::chrono::steady_clock::now();
+                    fprintf(stderr, "[lsb trace] q%d +%8.3f ms flush %4zu units in %7.3f ms (feeding %d)\n",
+                            q, std::chrono::duration<double, std::milli>(f0 - t_start).count(), np,
+                            std::chrono::duration<double, std::milli>(f1 - f0).count(), flying);
+                }
+            }
         }
     }
+    if (trace)
+        fprintf(stderr, "[lsb trace] q%d dispatch done at +%.3f ms\n", q,
+                std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count());
 }
 
 static int run_task(GpuTask& task, CArgument* input_args, uint64_t n_in, CArgument* output_args, uint64_t n_out,
@@ -1473,17 +1504,37 @@ static int run_task(GpuTask& task, CArgument* input_args, uint64_t n_in, CArgume
             }
         }
     }
+    rs.ready_q.assign(devs.size(), {});
     rs.remaining.assign(task.plan.units.size(), 0);
     for (const Unit& u : task.plan.units) {
         int missing = 0;
         for (DatumNode* in : u.ext_inputs)
             if (!rs.avail.count(in->index)) missing++;
         rs.remaining[u.id] = missing;
-        if (missing == 0) rs.ready.push_back(u.id);
+        if (missing == 0) rs.ready_q[rs.queue_of(u.id)].push_back(u.id);
     }
     for (auto& kv : task.plan.consumers) rs.refcnt[kv.first] = (int)kv.second.size();
 
-    rs.dispatch();
+    // one dispatcher per device (each GPU has its own scheduler): components never span devices, so the
+    // queues are independent; the caller's thread serves device slot 0 and the host-only units
+    {
+        auto serve = [&rs](int q) {
+            try {
+                rs.dispatch(q);
+            } catch (const std::exception& e) {
+                rs.fail(std::string("dispatcher: ") + e.what());
+                {
+                    std::lock_guard<std::mutex> lk(rs.mu);
+                    rs.aborted = true;
+                }
+                rs.cv.notify_all();
+            }
+        };
+        std::vector<std::thread> others;
+        for (int q = 1; q < (int)devs.size(); q++) others.emplace_back(serve, q);
+        serve(0);
+        for (auto& t : others) t.join();
+    }
 
     for (DeviceRuntime* rt : rs.slots) {
         LSB_CUDA(cudaSetDevice(rt->device));

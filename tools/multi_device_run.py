@@ -24,9 +24,12 @@ if __name__ == "__main__":
             task = h.th_open(gc.path.encode(), 1)
             best = 1e9
             for rep in range(4):
+                if rep == 3 and os.environ.get("MD_TRACE"):
+                    os.environ["LSB_TRACE"] = "1"
                 t = time.time()
                 out = gc.run(task=task, devices=list(range(n)))
                 best = min(best, time.time() - t)
+                os.environ.pop("LSB_TRACE", None)
             d = GE.digest(out)
             ref = ref or d
             print("devices %d: %.1f ms per call, %.0f polynomial evaluations/s, stats %s, outputs %s" %

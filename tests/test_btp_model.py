@@ -73,3 +73,29 @@ def test_eval_mod_model_removes_the_q0_multiples():
     got = B.eval_mod_model(msg + k)
     assert np.abs(got - np.sin(2 * np.pi * msg) / (2 * np.pi)).max() < 2.0 ** -22
     assert np.abs(got - msg).max() < 2.0 ** -14          # sin(x) ~ x: the inherent message_ratio error
+
+
+def _toy_case():
+    import btp_pipeline as P
+    import fhe_ref as R
+    prm = P.toy_params(10, 16)
+    orc = R.Oracle(prm)
+    secret = P.sparse_secret(orc.N, 32, 5)
+    rng = np.random.default_rng(1)
+    z = (rng.uniform(-1, 1, orc.N // 2) + 1j * rng.uniform(-1, 1, orc.N // 2)) * 0.5
+    delta = 2.0 ** 45
+    ct0 = P.Ct(orc.encrypt(secret, 3, 0, R.ckks_encode(orc, z, 0, delta)), delta)
+    return P, R, prm, orc, secret, z, ct0
+
+
+def test_toy_bootstrap_on_the_oracle_recovers_the_message():
+    """N=2^10, 17 primes of 55 bits, sparse secret: a level-0 ciphertext comes back at level 3 with the reference's
+    acceptance criterion met (mean real precision >= 10 bits, test_gpu_ckks.cpp:37-43,743-808)."""
+    P, R, prm, orc, secret, z, ct0 = _toy_case()
+    ev = P.Evaluator(orc, secret)
+    out = P.bootstrap(ev, ct0)
+    res = ev.decode(out, secret)
+    assert out.level == 3
+    assert R.mean_precision_bits(res, z) >= 16.0
+    assert np.abs(res - z).max() < 1e-4
+    assert ev.counts["rotate"] > 150 and ev.counts["mult"] == 28

@@ -75,10 +75,10 @@ def test_eval_mod_model_removes_the_q0_multiples():
     assert np.abs(got - msg).max() < 2.0 ** -14          # sin(x) ~ x: the inherent message_ratio error
 
 
-def _toy_case():
+def _toy_case(log_n=10, levels=16):
     import btp_pipeline as P
     import fhe_ref as R
-    prm = P.toy_params(10, 16)
+    prm = P.toy_params(log_n, levels)
     orc = R.Oracle(prm)
     secret = P.sparse_secret(orc.N, 32, 5)
     rng = np.random.default_rng(1)

@@ -272,18 +272,18 @@ def test_errors_are_reported_not_swallowed():
 
 @pytest.mark.gpu
 def test_toy_bootstrap_device_ops_equal_the_oracle_limb_for_limb():
-    """The whole bootstrapping pipeline of tests/btp_pipeline.py (ModRaise, CoeffsToSlots, EvalMod, SlotsToCoeffs: 188
-    rotations / conjugations, 28 ct x ct + relin, 42 rescales, 55-bit primes, 13 levels deep) run twice on the same
-    keys: once on the oracle, once with every ciphertext operation on the device through lsb200.h.  Output limbs must be
+    """The whole bootstrapping pipeline of tests/btp_pipeline.py at N=2^12 (ModRaise, CoeffsToSlots, EvalMod,
+    SlotsToCoeffs: 154 rotations / conjugations, 28 ct x ct + relin, 44 rescales, 55-bit primes, 15 levels deep) run
+    twice on the same keys: once on the oracle, once with every ciphertext operation on the device through lsb200.h.  Output limbs must be
     identical and decode to the input within the reference's bootstrapping criterion."""
     import btp_pipeline as P
     import test_btp_model as TB
 
-    _, R, prm, orc, secret, z, ct0 = TB._toy_case()
-    want = P.bootstrap(P.Evaluator(orc, secret), ct0)
+    _, R, prm, orc, secret, z, ct0 = TB._toy_case(12, 17)  # the device supports N >= 2^12
+    want = P.bootstrap(P.Evaluator(orc, secret), ct0, cts_depth=3, stc_depth=3)
     ctx = _ctx(prm)
     ev = P.Evaluator(orc, secret, ops=ctx)
-    got = P.bootstrap(ev, ct0)
-    assert got.level == want.level == 3
+    got = P.bootstrap(ev, ct0, cts_depth=3, stc_depth=3)
+    assert got.level == want.level == 2
     assert np.array_equal(got.data, want.data)
-    assert R.mean_precision_bits(ev.decode(got, secret), z) >= 16.0
+    assert R.mean_precision_bits(ev.decode(got, secret), z) >= 12.0

@@ -68,6 +68,11 @@ int lsb_relin(lsb_context_t ctx, int level, const uint64_t* d_ct3, const uint64_
 int lsb_rescale(lsb_context_t ctx, int level, int npoly, const uint64_t* d_in, uint64_t* d_out, int batch,
                 void* stream);
 /* bind_gpu_drop_level (mega_ag_executors_gpu.cu:250-262). */
+/* CKKS ModRaise, the first step of bootstrapping (reference: CkksBtpContext::bootstrap behind
+ * mega_ag_executors_gpu.cu:410-426 / mega_ag_executors_cpu.cpp:451-468; Lattigo ckks/bootstrapping): level-0
+ * ciphertext [npoly][1][N] -> [npoly][top_level+1][N], the centred residues mod q_0 re-read modulo every prime. */
+int lsb_mod_raise(lsb_context_t ctx, int top_level, int npoly, const uint64_t* d_in, uint64_t* d_out, int batch,
+                  void* stream);
 int lsb_drop_level(lsb_context_t ctx, int level, int npoly, const uint64_t* d_in, uint64_t* d_out, int batch,
                    void* stream);
 /* bind_gpu_rotate_col / bind_gpu_rotate_row (mega_ag_executors_gpu.cu:264-292): automorphism X -> X^gal

@@ -59,6 +59,7 @@ def lib():
     L.lsb_relin.argtypes = [vp, ci, vp, vp, ci, vp, ci, vp]
     L.lsb_rescale.argtypes = [vp, ci, ci, vp, vp, ci, vp]
     L.lsb_drop_level.argtypes = [vp, ci, ci, vp, vp, ci, vp]
+    L.lsb_mod_raise.argtypes = [vp, ci, ci, vp, vp, ci, vp]
     L.lsb_rotate.argtypes = [vp, ci, vp, vp, ci, C.c_uint64, vp, ci, vp]
     L.lsb_add.argtypes = [vp, ci, ci, vp, vp, vp, ci, vp]
     L.lsb_sub.argtypes = [vp, ci, ci, vp, vp, vp, ci, vp]
@@ -243,6 +244,15 @@ class Context:
         ct, single = self._batch(ct, 3)
         B, npoly, l, N = ct.shape
         r = self._run(lambda bf, o: self.rescale_dev(l - 1, npoly, bf[0], o, B), [ct], (B, npoly, l - 1, N))
+        return r[0] if single else r
+
+    def mod_raise(self, ct0, top_level):
+        """level-0 ciphertext [2][1][N] -> [2][top_level+1][N] (bootstrapping ModRaise)"""
+        ct0, single = self._batch(ct0, 3)
+        B, npoly, l, N = ct0.shape
+        assert l == 1
+        r = self._run(lambda bf, o: _check(lib().lsb_mod_raise(self.h, top_level, npoly, bf[0].ptr, o.ptr, B, self.stream)),
+                      [ct0], (B, npoly, top_level + 1, N))
         return r[0] if single else r
 
     def drop_level(self, ct):

@@ -144,6 +144,11 @@ int lsb_rescale(lsb_context_t h, int level, int npoly, const uint64_t* d_in, uin
                    dense(d_out, e.c.ct_words(level - 1, npoly)), batch);
     });
 }
+int lsb_mod_raise(lsb_context_t h, int top_level, int npoly, const uint64_t* d_in, uint64_t* d_out, int batch, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        op_mod_raise(e, top_level, npoly, dense(d_in, e.c.ct_words(0, npoly)), dense(d_out, e.c.ct_words(top_level, npoly)), batch);
+    });
+}
 int lsb_drop_level(lsb_context_t h, int level, int npoly, const uint64_t* d_in, uint64_t* d_out, int batch,
                    void* stream) {
     return run_op(h, stream, [&](OpEnv& e) {

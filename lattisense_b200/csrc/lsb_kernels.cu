@@ -497,23 +497,29 @@ void launch_ks_inner(const DeviceTables& dt, const KsInnerArgs& a, int batch, cu
 // ---- rescale ---------------------------------------------------------------------------------------------
 struct RescaleLiftArgs {
     BatchPtr last, tmp;
-    int N, npoly, level, last_ps;
+    int N, npoly, level, last_ps, raise;
     const ModConst* mods;
 };
-// last: coefficient-domain limb `level` of each polynomial (block [npoly] with stride last_ps limbs)
+// last: coefficient-domain limb of each polynomial (block [npoly] with stride last_ps limbs), residues of the SOURCE
+// modulus: q_level for the rescale (targets q_0..q_{level-1}), q_0 for ModRaise (raise = 1: targets q_1..q_level, the
+// source limb is kept as limb 0 of the result).  Each target gets the CENTRED lift reduced: ((x + half) mod q_src
+// reduced mod q_i) - half mod q_i.
 template <bool F64>
 __global__ void __launch_bounds__(kElemThreads) k_rescale_lift(const __grid_constant__ RescaleLiftArgs g) {
     const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
     if (j2 >= g.N / 2) return;
     const int p = blockIdx.y, b = blockIdx.z;
-    const u64 ql = g.mods[g.level].q, half = (ql - 1) >> 1;
-    W2 x = ld2(g.last.at(b) + (size_t)p * g.last_ps * g.N, j2);
-    x.a = addmod(x.a, half, ql);
-    x.b = addmod(x.b, half, ql);
-    u64* pt = g.tmp.at(b) + (size_t)p * g.level * g.N;
+    const u64 ql = g.mods[g.raise ? 0 : g.level].q, half = (ql - 1) >> 1;
+    const W2 x0 = ld2(g.last.at(b) + (size_t)p * g.last_ps * g.N, j2);
+    W2 x;
+    x.a = addmod(x0.a, half, ql);
+    x.b = addmod(x0.b, half, ql);
+    const int i0 = g.raise ? 1 : 0, i1 = g.raise ? g.level + 1 : g.level;
+    u64* pt = g.tmp.at(b) + (size_t)p * i1 * g.N;
+    if (g.raise) st2(pt, j2, x0);
     if constexpr (F64) {  // every prime below 2^47: the per-target reductions on the FP64 pipe (integer version: IMAD-bound)
         const double xa = f64_from_u64(x.a), xb = f64_from_u64(x.b);
-        for (int i = 0; i < g.level; i++) {
+        for (int i = i0; i < i1; i++) {
             const ModConst& m = g.mods[i];
             const double hq = f64_from_u64(barrett64(half, m.bq));  // CTA-uniform
             W2 o;
@@ -523,7 +529,7 @@ __global__ void __launch_bounds__(kElemThreads) k_rescale_lift(const __grid_cons
         }
         return;
     }
-    for (int i = 0; i < g.level; i++) {
+    for (int i = i0; i < i1; i++) {
         const ModConst& m = g.mods[i];
         const u64 hq = barrett64(half, m.bq);  // CTA-uniform
         W2 o;
@@ -533,9 +539,9 @@ __global__ void __launch_bounds__(kElemThreads) k_rescale_lift(const __grid_cons
     }
 }
 void launch_rescale_lift(const DeviceTables& dt, BatchPtr last, int last_poly_stride, BatchPtr tmp, int npoly, int level,
-                         int batch, cudaStream_t s) {
+                         int batch, cudaStream_t s, bool raise) {
     if (batch <= 0) return;
-    RescaleLiftArgs g{last, tmp, dt.N, npoly, level, last_poly_stride, dt.mods};
+    RescaleLiftArgs g{last, tmp, dt.N, npoly, level, last_poly_stride, raise ? 1 : 0, dt.mods};
     ProfScope _ps(dt.prof, PK_ELEMWISE, s, 8.0 * dt.N * npoly * batch * (1 + level));
     bool f64 = elem_f64_enabled();
     for (int i = 0; i <= level; i++) f64 = f64 && dt.elem_f64_ok[i];

@@ -125,7 +125,7 @@ void launch_ks_inner(const DeviceTables& dt, const KsInnerArgs& a, int batch, cu
 
 // CKKS rescale lift: tmp[p][i] = ((last[p] + half) mod q_i) - half mod q_i, i < level
 void launch_rescale_lift(const DeviceTables& dt, BatchPtr last, int last_poly_stride, BatchPtr tmp, int npoly, int level,
-                         int batch, cudaStream_t s);
+                         int batch, cudaStream_t s, bool raise = false);
 // BFV rescale (coefficient domain, fully fused): [np][l] -> [np][l-1]
 void launch_bfv_rescale(const DeviceTables& dt, BatchPtr in, BatchPtr out, int npoly, int level, const Tw* qlinv_dev,
                         int batch, cudaStream_t s);

@@ -315,6 +315,27 @@ void op_rescale(OpEnv& e, int level, int npoly, BatchPtr in, BatchPtr out, int b
     }
 }
 
+// CKKS ModRaise (first step of bootstrapping; Lattigo ckks/bootstrapping `modUpFromQ0`): a level-0 ciphertext
+// [npoly][1][N] (NTT domain) is re-read modulo q_0..q_top -- INTT of the q_0 limb, centred lift to every other prime,
+// NTT of all limbs -- and comes out at level `top` encrypting Delta*m + q_0*I.
+void op_mod_raise(OpEnv& e, int top, int npoly, BatchPtr in, BatchPtr out, int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    Context& c = e.c;
+    LSB_CHECK(c.scheme == SCHEME_CKKS, "lsb: mod_raise is a CKKS operation");
+    LSB_CHECK(top >= 1 && top < c.nq && npoly >= 1 && npoly * (top + 1) <= kMaxRows, "lsb: mod_raise: bad level");
+    const int l = top + 1;
+    const size_t item = (size_t)npoly * c.N;
+    const int chunk = pick_chunk(e, item, batch, npoly * l);
+    u64* scratch = e.ws.reserve(item * chunk, e.s);
+    for (int b0 = 0; b0 < batch; b0 += chunk) {
+        const int nb = std::min(chunk, batch - b0);
+        BatchPtr last = bp_strided(scratch, item);
+        launch_ntt(c.dt, adv(in, b0), last, rowmap_seq(npoly, 0, 0, 0, 1), nb, true, e.s);
+        launch_rescale_lift(c.dt, last, 1, adv(out, b0), npoly, top, nb, e.s, true);
+        launch_ntt(c.dt, adv(out, b0), adv(out, b0), rowmap_seq(npoly * l, 0, 0, 0, l), nb, false, e.s);
+    }
+}
+
 void op_drop_level(OpEnv& e, int level, int npoly, BatchPtr in, BatchPtr out, int batch) {
     LSB_CUDA(cudaSetDevice(e.c.device));
     LSB_CHECK(level >= 1, "lsb: cannot drop below level 0");

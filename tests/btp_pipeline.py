@@ -164,6 +164,8 @@ class Evaluator:
 def mod_raise(ev, ct0):
     """level-0 ciphertext -> top level: the centred residues mod q0 re-read modulo every prime (Lattigo `ModRaise`).
     The result encrypts Delta*m + q0*I with a small integer polynomial I (|I| grows with the secret's weight)."""
+    if hasattr(ev.ops, "mod_raise"):  # the device has it as one operation (lsb_mod_raise)
+        return Ct(ev.ops.mod_raise(ct0.data, ev.top), ct0.scale)
     q0 = ev.q[0]
     coef = ev.ops.ntt(ct0.data, [0], inverse=True)
     out = np.zeros((2, ev.top + 1, ev.N), dtype=np.uint64)

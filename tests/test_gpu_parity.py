@@ -287,3 +287,20 @@ def test_toy_bootstrap_device_ops_equal_the_oracle_limb_for_limb():
     assert got.level == want.level == 2
     assert np.array_equal(got.data, want.data)
     assert R.mean_precision_bits(ev.decode(got, secret), z) >= 12.0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("params", [R.CKKS_N13, R.CKKS_WIDE_N13, R.CKKS_BTP_N13], ids=lambda p: p.name)
+def test_mod_raise_parity(params):
+    """lsb_mod_raise against the pipeline's ModRaise on the oracle (centred residues mod q0 re-read mod every prime)."""
+    import btp_pipeline as P
+
+    o, ctx, s = env(params)
+    rng = np.random.default_rng(21)
+    top = len(params.q) - 1
+    ct0 = rand_ct(o, rng, 0, batch=3)
+    ev = P.Evaluator(o, s)
+    want = np.stack([P.mod_raise(ev, P.Ct(ct0[b], 1.0)).data for b in range(3)])
+    got = ctx.mod_raise(ct0, top)
+    assert got.shape == want.shape == (3, 2, top + 1, o.N)
+    assert np.array_equal(got, want)

@@ -73,6 +73,14 @@ int lsb_rescale(lsb_context_t ctx, int level, int npoly, const uint64_t* d_in, u
  * ciphertext [npoly][1][N] -> [npoly][top_level+1][N], the centred residues mod q_0 re-read modulo every prime. */
 int lsb_mod_raise(lsb_context_t ctx, int top_level, int npoly, const uint64_t* d_in, uint64_t* d_out, int batch,
                   void* stream);
+/* Diagonal-form linear transform, baby-step / giant-step: the CoeffsToSlots / SlotsToCoeffs matrices of CKKS
+ * bootstrapping (rotation sets: frontend/bootstrap_params.py:159-209).  diag_rot[i] = diagonal index k_i;
+ * d_diag_pt[i] = its plaintext [level+1][N], NTT domain, slot values rotated by -(k_i - k_i mod n1) at encode time;
+ * key_rot / d_glk = the column-rotation keys at hand (rotation amount -> key, all at key_level).
+ * out = rescale(sum_g rot(sum_b pt_{g+b} * rot(ct, b), g)) at level-1.  One ciphertext per call. */
+int lsb_linear_transform(lsb_context_t ctx, int level, const uint64_t* d_ct, int n_diag, const int* diag_rot,
+                         const uint64_t* const* d_diag_pt, int n1, int n_keys, const int* key_rot,
+                         const uint64_t* const* d_glk, int key_level, uint64_t* d_out, void* stream);
 int lsb_drop_level(lsb_context_t ctx, int level, int npoly, const uint64_t* d_in, uint64_t* d_out, int batch,
                    void* stream);
 /* bind_gpu_rotate_col / bind_gpu_rotate_row (mega_ag_executors_gpu.cu:264-292): automorphism X -> X^gal

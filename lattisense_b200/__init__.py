@@ -60,6 +60,7 @@ def lib():
     L.lsb_rescale.argtypes = [vp, ci, ci, vp, vp, ci, vp]
     L.lsb_drop_level.argtypes = [vp, ci, ci, vp, vp, ci, vp]
     L.lsb_mod_raise.argtypes = [vp, ci, ci, vp, vp, ci, vp]
+    L.lsb_linear_transform.argtypes = [vp, ci, vp, ci, vp, vp, ci, ci, vp, vp, ci, vp, vp]
     L.lsb_rotate.argtypes = [vp, ci, vp, vp, ci, C.c_uint64, vp, ci, vp]
     L.lsb_add.argtypes = [vp, ci, ci, vp, vp, vp, ci, vp]
     L.lsb_sub.argtypes = [vp, ci, ci, vp, vp, vp, ci, vp]
@@ -254,6 +255,30 @@ class Context:
         r = self._run(lambda bf, o: _check(lib().lsb_mod_raise(self.h, top_level, npoly, bf[0].ptr, o.ptr, B, self.stream)),
                       [ct0], (B, npoly, top_level + 1, N))
         return r[0] if single else r
+
+    def linear_transform(self, ct, plan, n1, keys):
+        """BSGS diagonal-form linear transform + rescale (lsb_linear_transform).  plan: [(diagonal index k, plaintext
+        [l][N] NTT, slot values pre-rotated by -(k - k % n1))]; keys: {column rotation: evaluation key array}."""
+        ct = np.ascontiguousarray(ct, dtype=np.uint64)
+        _, l, N = ct.shape
+        level = l - 1
+        d_ct = self.upload(ct)
+        d_pts = [self.upload(pt) for _, pt in plan]
+        rots = sorted(keys)
+        d_keys = [self.upload(keys[r]) for r in rots]
+        key_level = (keys[rots[0]].shape[2] - self.k - 1) if rots else level
+        n, nk = len(plan), len(rots)
+        diag_rot = (C.c_int * n)(*[int(k) for k, _ in plan])
+        diag_ptr = (C.c_void_p * n)(*[b.ptr for b in d_pts])
+        key_rot = (C.c_int * max(nk, 1))(*rots)
+        key_ptr = (C.c_void_p * max(nk, 1))(*[b.ptr for b in d_keys])
+        out = DevBuf(self, 2 * level * N)
+        _check(lib().lsb_linear_transform(self.h, level, d_ct.ptr, n, diag_rot, diag_ptr, n1, nk, key_rot, key_ptr, key_level,
+                                          out.ptr, self.stream))
+        res = self.download(out, (2, level, N))
+        for b in [d_ct, out] + d_pts + d_keys:
+            b.free()
+        return res
 
     def drop_level(self, ct):
         ct, single = self._batch(ct, 3)

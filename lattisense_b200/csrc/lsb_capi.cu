@@ -149,6 +149,13 @@ int lsb_mod_raise(lsb_context_t h, int top_level, int npoly, const uint64_t* d_i
         op_mod_raise(e, top_level, npoly, dense(d_in, e.c.ct_words(0, npoly)), dense(d_out, e.c.ct_words(top_level, npoly)), batch);
     });
 }
+int lsb_linear_transform(lsb_context_t h, int level, const uint64_t* d_ct, int n_diag, const int* diag_rot,
+                         const uint64_t* const* d_diag_pt, int n1, int n_keys, const int* key_rot, const uint64_t* const* d_glk,
+                         int key_level, uint64_t* d_out, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        op_linear_transform(e, level, d_ct, n_diag, diag_rot, d_diag_pt, n1, n_keys, key_rot, d_glk, key_level, d_out);
+    });
+}
 int lsb_drop_level(lsb_context_t h, int level, int npoly, const uint64_t* d_in, uint64_t* d_out, int batch,
                    void* stream) {
     return run_op(h, stream, [&](OpEnv& e) {

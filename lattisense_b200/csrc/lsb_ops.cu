@@ -336,6 +336,101 @@ void op_mod_raise(OpEnv& e, int top, int npoly, BatchPtr in, BatchPtr out, int b
     }
 }
 
+// Diagonal-form linear transform, baby-step / giant-step (the CoeffsToSlots / SlotsToCoeffs matrices of bootstrapping;
+// frontend/bootstrap_params.py:159-209 fixes the split and the rotation set):
+//   out = rescale( sum_g rot( sum_b pt_{g,b} * rot(ct, b), g ) ),   diagonal k = g + b, b = k mod n1,
+// with the plaintexts already rotated by -g and in the NTT domain at `level`.  Every inner sum is one multiply-accumulate
+// pass (k_sum_terms), the outer sum another; rotations are the ordinary key switches (hoisting is the next step).
+void op_linear_transform(OpEnv& e, int level, const u64* ct, int n_diag, const int* diag_rot, const u64* const* diag_pt, int n1,
+                         int n_keys, const int* key_rot, const u64* const* glk, int key_level, u64* out) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    Context& c = e.c;
+    LSB_CHECK(c.scheme == SCHEME_CKKS && level >= 1 && level < c.nq && n_diag >= 1 && n1 >= 1, "lsb: linear_transform: bad arguments");
+    const int slots = c.N / 2, l = level + 1;
+    const size_t words = (size_t)2 * l * c.N;
+    auto key_for = [&](int rot) -> const u64* {
+        for (int i = 0; i < n_keys; i++)
+            if (key_rot[i] == rot) return glk[i];
+        throw std::runtime_error("lsb: linear_transform: no Galois key for rotation " + std::to_string(rot));
+    };
+    auto gal_of = [&](int rot) {
+        const u64 m = 2ull * c.N;
+        u64 r = 1, b = 5 % m;
+        for (int x = rot; x; x >>= 1, b = b * b % m)
+            if (x & 1) r = r * b % m;
+        return r;
+    };
+    std::vector<int> babies, giants;
+    for (int i = 0; i < n_diag; i++) {
+        const int k = ((diag_rot[i] % slots) + slots) % slots, b = k % n1, g = k - b;
+        if (std::find(babies.begin(), babies.end(), b) == babies.end()) babies.push_back(b);
+        if (std::find(giants.begin(), giants.end(), g) == giants.end()) giants.push_back(g);
+    }
+    std::sort(giants.begin(), giants.end());
+    // device buffers: rotated inputs, one accumulator per giant step, pointer tables
+    u64* pool = nullptr;
+    const size_t n_buf = babies.size() + 2 * giants.size() + 1;
+    LSB_CUDA(cudaMallocAsync((void**)&pool, n_buf * words * sizeof(u64), e.s));
+    const u64** tab = nullptr;
+    const size_t tab_len = 2 * (size_t)n_diag + giants.size() + 2;
+    LSB_CUDA(cudaMallocAsync((void**)&tab, tab_len * sizeof(u64*), e.s));
+    size_t next = 0;
+    auto take = [&] { return pool + (next++) * words; };
+    std::vector<const u64*> baby_ptr(babies.size());
+    for (size_t i = 0; i < babies.size(); i++) {
+        if (babies[i] == 0) {
+            baby_ptr[i] = ct;
+            continue;
+        }
+        u64* dst = take();
+        op_rotate(e, level, bp_strided(ct, words), key_for(babies[i]), key_level, gal_of(babies[i]), bp_strided(dst, words), 1);
+        baby_ptr[i] = dst;
+    }
+    std::vector<const u64*> host_tab;
+    std::vector<const u64*> giant_out;
+    size_t tab_used = 0;
+    auto upload = [&](const std::vector<const u64*>& v) {
+        const u64** d = tab + tab_used;
+        LSB_CUDA(cudaMemcpyAsync(d, v.data(), v.size() * sizeof(u64*), cudaMemcpyHostToDevice, e.s));
+        tab_used += v.size();
+        return d;
+    };
+    for (int g : giants) {
+        std::vector<const u64*> cts, pts;
+        for (int i = 0; i < n_diag; i++) {
+            const int k = ((diag_rot[i] % slots) + slots) % slots;
+            if (k - k % n1 != g) continue;
+            const size_t bi = std::find(babies.begin(), babies.end(), k % n1) - babies.begin();
+            cts.push_back(baby_ptr[bi]);
+            pts.push_back(diag_pt[i]);
+        }
+        u64* acc = take();
+        std::vector<const u64*> o{acc};
+        const u64** d_ct = upload(cts);
+        const u64** d_pt = upload(pts);
+        const u64** d_o = upload(o);
+        launch_sum_terms(c.dt, d_ct, d_pt, (u64* const*)d_o, 2, l, (int)cts.size(), 0, 1, e.s);
+        if (g == 0) {
+            giant_out.push_back(acc);
+        } else {
+            u64* r = take();
+            op_rotate(e, level, bp_strided(acc, words), key_for(g), key_level, gal_of(g), bp_strided(r, words), 1);
+            giant_out.push_back(r);
+        }
+    }
+    u64* total = take();
+    {
+        std::vector<const u64*> o{total};
+        const u64** d_ct = upload(giant_out);
+        const u64** d_o = upload(o);
+        launch_sum_terms(c.dt, d_ct, nullptr, (u64* const*)d_o, 2, l, 0, (int)giant_out.size(), 1, e.s);
+    }
+    LSB_CHECK(tab_used <= tab_len && next <= n_buf, "lsb: linear_transform: internal buffer accounting");
+    op_rescale(e, level, 2, bp_strided(total, words), bp_strided(out, (size_t)2 * level * c.N), 1);
+    LSB_CUDA(cudaFreeAsync(pool, e.s));
+    LSB_CUDA(cudaFreeAsync(tab, e.s));
+}
+
 void op_drop_level(OpEnv& e, int level, int npoly, BatchPtr in, BatchPtr out, int batch) {
     LSB_CUDA(cudaSetDevice(e.c.device));
     LSB_CHECK(level >= 1, "lsb: cannot drop below level 0");

@@ -23,6 +23,8 @@ void op_relin(OpEnv& e, int level, BatchPtr ct3, const u64* rlk, int key_level, 
 void op_rescale(OpEnv& e, int level, int npoly, BatchPtr in, BatchPtr out, int batch);
 // bind_gpu_drop_level (:250-262)
 void op_mod_raise(OpEnv& e, int top_level, int npoly, BatchPtr in, BatchPtr out, int batch);
+void op_linear_transform(OpEnv& e, int level, const u64* ct, int n_diag, const int* diag_rot, const u64* const* diag_pt, int n1,
+                         int n_keys, const int* key_rot, const u64* const* glk, int key_level, u64* out);
 void op_drop_level(OpEnv& e, int level, int npoly, BatchPtr in, BatchPtr out, int batch);
 // bind_gpu_rotate_col / bind_gpu_rotate_row (:264-292): automorphism gal + key-switch under glk[gal]
 void op_rotate(OpEnv& e, int level, BatchPtr ct, const u64* glk, int key_level, u64 gal, BatchPtr out, int batch);

@@ -77,7 +77,9 @@ class Evaluator:
 
     def _key(self, gal):
         if gal not in self.glk:
-            self.glk[gal] = self.o.gen_glk(self.s, self.seed + 1 + len(self.glk), self.top, gal)
+            # the key's randomness depends on the Galois element only, so that two runs that ask for keys in a
+            # different order (oracle ops one by one, device op per matrix) use identical keys
+            self.glk[gal] = self.o.gen_glk(self.s, self.seed + 1 + gal % 1000003, self.top, gal)
         return self.glk[gal]
 
     def rotate(self, ct, k):
@@ -143,18 +145,30 @@ class Evaluator:
         return R.ckks_decode_coeffs(coeffs, self.N, ct.scale)
 
     # ---- linear transform, baby-step / giant-step ----
+    def linear_plan(self, level, diags, n1, pt_scale, factor=1.0):
+        """[(k, encoded diagonal k rotated by -(giant step of k))] -- what a bootstrapping context precomputes."""
+        return [(k, R.ckks_encode(self.o, np.roll(d, (k // n1) * n1) * factor, level, pt_scale)) for k, d in sorted(diags.items())]
+
     def linear(self, ct, diags, n1, pt_scale, factor=1.0):
-        """sum_g rot( sum_b encode(rot(d_{g+b}, -g) * factor) * rot(ct, b), g ), then one rescale."""
-        n = self.n
+        """sum_g rot( sum_b pt_{g+b} * rot(ct, b), g ), then one rescale."""
+        plan = self.linear_plan(ct.level, diags, n1, pt_scale, factor)
+        if hasattr(self.ops, "linear_transform"):  # one device operation (lsb_linear_transform)
+            rots = {r for k, _ in plan for r in (k % n1, (k // n1) * n1) if r}
+            keys = {r: self._key(R.galois_for_col_step(self.N, r)) for r in rots}
+            self.counts["rotate"] += len(rots)
+            self.counts["mul_plain"] += len(plan)
+            self.counts["rescale"] += 1
+            return Ct(self.ops.linear_transform(ct.data, plan, n1, keys), ct.scale * pt_scale / self.q[ct.level])
         groups = {}
-        for k, d in diags.items():
-            groups.setdefault((k // n1) * n1, []).append((k % n1, d))
+        for k, pt in plan:
+            groups.setdefault((k // n1) * n1, []).append((k % n1, pt))
         baby = {b: self.rotate(ct, b) for items in groups.values() for b, _ in items}
         total = None
         for g, items in sorted(groups.items()):
             acc = None
-            for b, d in items:
-                term = self.mul_vec(baby[b], np.roll(d, g) * factor, pt_scale)
+            for b, pt in items:
+                self.counts["mul_plain"] += 1
+                term = Ct(self.ops.mul_plain(baby[b].data, pt), ct.scale * pt_scale)
                 acc = term if acc is None else self.add(acc, term)
             acc = self.rotate(acc, g)
             total = acc if total is None else self.add(total, acc)

@@ -304,3 +304,28 @@ def test_mod_raise_parity(params):
     got = ctx.mod_raise(ct0, top)
     assert got.shape == want.shape == (3, 2, top + 1, o.N)
     assert np.array_equal(got, want)
+
+
+@pytest.mark.gpu
+def test_linear_transform_parity():
+    """lsb_linear_transform (BSGS: rotations, one multiply-accumulate pass per giant step, rescale) against the same
+    matrix evaluated op by op on the oracle; the matrix is a merged CoeffsToSlots factor (tests/btp_model.py)."""
+    import btp_model as B
+    import btp_pipeline as P
+
+    prm = P.toy_params(12, 4)
+    o = R.Oracle(prm)
+    secret = P.sparse_secret(o.N, 32, 9)
+    n = o.N // 2
+    rng = np.random.default_rng(5)
+    z = rng.uniform(-1, 1, n) + 1j * rng.uniform(-1, 1, n)
+    ct = P.Ct(o.encrypt(secret, 4, 4, R.ckks_encode(o, z, 4, 2.0 ** 45)), 2.0 ** 45)
+    mats = B.factor_c2s(n, 3)
+    idx = B.dft_index_map(n.bit_length() - 1, 3, True)
+    for m, ix in zip(mats[:2], idx[:2]):
+        n1 = B.bsgs_split(ix, n, 2.0)
+        want = P.Evaluator(o, secret).linear(ct, m, n1, float(prm.q[4]))
+        ev = P.Evaluator(o, secret, ops=_ctx(prm))
+        got = ev.linear(ct, m, n1, float(prm.q[4]))
+        assert np.array_equal(got.data, want.data)
+        assert np.abs(ev.decode(got, secret) - B.apply(m, z)).max() < 1e-6

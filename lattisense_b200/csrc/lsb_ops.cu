@@ -372,7 +372,7 @@ void op_linear_transform(OpEnv& e, int level, const u64* ct, int n_diag, const i
     const size_t n_buf = babies.size() + 2 * giants.size() + 1;
     LSB_CUDA(cudaMallocAsync((void**)&pool, n_buf * words * sizeof(u64), e.s));
     const u64** tab = nullptr;
-    const size_t tab_len = 2 * (size_t)n_diag + giants.size() + 2;
+    const size_t tab_len = 2 * (size_t)n_diag + 2 * giants.size() + 2;
     LSB_CUDA(cudaMallocAsync((void**)&tab, tab_len * sizeof(u64*), e.s));
     size_t next = 0;
     auto take = [&] { return pool + (next++) * words; };

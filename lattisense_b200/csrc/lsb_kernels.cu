@@ -211,36 +211,71 @@ struct SumTermsArgs {
     u64* const* out;       // [batch]
     int N, nl, n_mac, n_plain, batch;
     const ModConst* mods;
+    // split > 1: the terms are cut into `split` ranges (chunk_mac / chunk_plain terms each), blockIdx.z = b * split + s
+    // writes its partial sum to partial[(b * split + s) * words]; k_sum_partials adds them up.  Gives a long sum of one
+    // ciphertext (12 800 terms in the convolution benchmark) enough CTAs to fill the machine.
+    int split, chunk_mac, chunk_plain;
+    u64* partial;
+    size_t words;
 };
 __global__ void __launch_bounds__(kElemThreads) k_sum_terms(const __grid_constant__ SumTermsArgs g) {
     const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
     if (j2 >= g.N / 2) return;
-    const int r = blockIdx.y, b = blockIdx.z, i = r % g.nl;
+    const int r = blockIdx.y, z = blockIdx.z, b = z / g.split, sp = z - b * g.split, i = r % g.nl;
     const BarrettQ bq = g.mods[i].bq;
     const size_t coff = (size_t)r * g.N, poff = (size_t)i * g.N;
+    const int m0 = min(g.n_mac, sp * g.chunk_mac), m1 = min(g.n_mac, m0 + g.chunk_mac);
+    const int p0 = min(g.n_plain, sp * g.chunk_plain), p1 = min(g.n_plain, p0 + g.chunk_plain);
     W2 acc{0, 0};
 #pragma unroll 4
-    for (int t = 0; t < g.n_mac; t++) {
+    for (int t = m0; t < m1; t++) {
         const W2 c = ld2(g.ct[(size_t)t * g.batch + b] + coff, j2);
         const W2 p = ld2(g.pt[(size_t)t * g.batch + b] + poff, j2);
         acc.a = addmod(acc.a, mulmod(c.a, p.a, bq), bq.q);
         acc.b = addmod(acc.b, mulmod(c.b, p.b, bq), bq.q);
     }
 #pragma unroll 4
-    for (int t = 0; t < g.n_plain; t++) {
+    for (int t = p0; t < p1; t++) {
         const W2 c = ld2(g.ct[(size_t)(g.n_mac + t) * g.batch + b] + coff, j2);
         acc.a = addmod(acc.a, c.a, bq.q);
         acc.b = addmod(acc.b, c.b, bq.q);
     }
+    u64* dst = g.split > 1 ? g.partial + (size_t)z * g.words : g.out[b];
+    st2(dst + coff, j2, acc);
+}
+__global__ void __launch_bounds__(kElemThreads) k_sum_partials(const __grid_constant__ SumTermsArgs g) {
+    const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j2 >= g.N / 2) return;
+    const int r = blockIdx.y, b = blockIdx.z;
+    const u64 q = g.mods[r % g.nl].q;
+    const size_t coff = (size_t)r * g.N;
+    W2 acc{0, 0};
+    for (int sp = 0; sp < g.split; sp++) {
+        const W2 c = ld2(g.partial + ((size_t)b * g.split + sp) * g.words + coff, j2);
+        acc.a = addmod(acc.a, c.a, q);
+        acc.b = addmod(acc.b, c.b, q);
+    }
     st2(g.out[b] + coff, j2, acc);
 }
+int sum_terms_split(const DeviceTables& dt, int npoly, int nl, int n_terms, int batch) {
+    const long ctas = (long)((dt.N / 2 + kElemThreads - 1) / kElemThreads) * npoly * nl * batch;
+    if (n_terms < 64 || ctas >= 4096) return 1;
+    return (int)std::min<long>((n_terms + 31) / 32, (8192 + ctas - 1) / ctas);
+}
 void launch_sum_terms(const DeviceTables& dt, const u64* const* ct, const u64* const* pt, u64* const* out, int npoly, int nl,
-                      int n_mac, int n_plain, int batch, cudaStream_t s) {
+                      int n_mac, int n_plain, int batch, cudaStream_t s, int split, u64* partial) {
     if (batch <= 0) return;
-    SumTermsArgs g{ct, pt, out, dt.N, nl, n_mac, n_plain, batch, dt.mods};
+    if (split < 1 || !partial) split = 1;
+    SumTermsArgs g{ct, pt, out, dt.N, nl, n_mac, n_plain, batch, dt.mods, split, (n_mac + split - 1) / split, (n_plain + split - 1) / split,
+                   partial, (size_t)npoly * nl * dt.N};
+    if (split == 1) g.chunk_mac = n_mac, g.chunk_plain = n_plain;
     ProfScope _ps(dt.prof, PK_ELEMWISE, s, 8.0 * dt.N * nl * batch * (npoly * (n_mac + n_plain + 1.0) + n_mac));
-    k_sum_terms<<<elem_grid(dt.N, npoly * nl, batch), kElemThreads, 0, s>>>(g);
+    k_sum_terms<<<elem_grid(dt.N, npoly * nl, batch * split), kElemThreads, 0, s>>>(g);
     LSB_CUDA(cudaGetLastError());
+    if (split > 1) {
+        k_sum_partials<<<elem_grid(dt.N, npoly * nl, batch), kElemThreads, 0, s>>>(g);
+        LSB_CUDA(cudaGetLastError());
+    }
 }
 
 // ---- basis extension -----------------------------------------------------------------------------

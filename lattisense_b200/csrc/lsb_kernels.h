@@ -83,8 +83,10 @@ void launch_negate(const DeviceTables& dt, BatchPtr a, BatchPtr out, const RowMa
 void launch_tensor(const DeviceTables& dt, BatchPtr a, BatchPtr b, BatchPtr out, int nl, int a_poly_stride,
                    int out_poly_stride, const uint8_t* mod_of_limb, int batch, cudaStream_t s);
 // out[p][i] (+)= ct[p][i] * pt[i]  (NTT domain), p < npoly
+// how many term ranges a sum should be cut into so that the launch fills the machine (1: no split)
+int sum_terms_split(const DeviceTables& dt, int npoly, int nl, int n_terms, int batch);
 void launch_sum_terms(const DeviceTables& dt, const u64* const* ct, const u64* const* pt, u64* const* out, int npoly, int nl,
-                      int n_mac, int n_plain, int batch, cudaStream_t s);
+                      int n_mac, int n_plain, int batch, cudaStream_t s, int split = 1, u64* partial = nullptr);
 void launch_mul_plain(const DeviceTables& dt, BatchPtr ct, BatchPtr pt, BatchPtr out, int npoly, int nl,
                       bool accumulate, int batch, cudaStream_t s);
 // out[r] = (a[a_slot[r]] - b[b_slot[r]]) * c_r (+ addend[add_slot[r]])   (ModDown / rescale finish)

@@ -625,7 +625,9 @@ void op_sum_terms(OpEnv& e, int level, int npoly, const u64* const* ct_tab, cons
     LSB_CUDA(cudaSetDevice(e.c.device));
     LSB_CHECK(level >= 0 && level < e.c.nq && npoly >= 1 && n_mac >= 0 && n_plain >= 0 && n_mac + n_plain >= 1, "lsb: sum_terms: bad arguments");
     LSB_CHECK(n_mac == 0 || e.c.scheme == SCHEME_CKKS, "lsb: sum_terms: fused products need NTT-domain (CKKS) operands");
-    launch_sum_terms(e.c.dt, ct_tab, pt_tab, out_tab, npoly, level + 1, n_mac, n_plain, batch, e.s);
+    const int split = sum_terms_split(e.c.dt, npoly, level + 1, n_mac + n_plain, batch);
+    u64* partial = split > 1 ? e.ws.reserve((size_t)split * batch * npoly * (level + 1) * e.c.N, e.s) : nullptr;
+    launch_sum_terms(e.c.dt, ct_tab, pt_tab, out_tab, npoly, level + 1, n_mac, n_plain, batch, e.s, split, partial);
 }
 
 // ---------------------------------------------------------------------------------------------

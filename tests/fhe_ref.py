@@ -16,6 +16,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORC_DIR = os.path.join(ROOT, "oracle")
 ORC_SO = os.path.join(ORC_DIR, "_build", "liborc.so")
+ORC_FAST_SO = os.path.join(ORC_DIR, "_build", "liborc_fast.so")
 
 SCHEME_BFV, SCHEME_CKKS = 0, 1
 
@@ -105,6 +106,76 @@ CKKS_WIDE_N13 = Params("ckks_wide_digit_n8192", SCHEME_CKKS, 13, CKKS_N14.q[:7],
 
 ALL_PARAMS = {p.name: p for p in (BFV_N14, BFV_N13, CKKS_N14, CKKS_N13, CKKS_BTP_N16, CKKS_BTP_N13, CKKS_BTP_N15, CKKS_N12,
                                      CKKS_WIDE_N13)}
+
+
+# ---------------------------------------------------------------------------------------------
+# Optimised CPU baseline (oracle/orc_fast.hpp): same algorithms with Shoup/Barrett lazy arithmetic, timed by bench.py's
+# reference arm; tests assert its limbs equal the simple oracle's
+# ---------------------------------------------------------------------------------------------
+_flib = None
+
+
+def fast_lib():
+    global _flib
+    if _flib is None:
+        if not os.path.exists(ORC_FAST_SO):
+            build_oracle()
+        _flib = C.CDLL(ORC_FAST_SO)
+        _flib.orcf_create.restype = C.c_void_p
+        _flib.orcf_create.argtypes = [C.c_int, C.c_int, u64p, C.c_int, u64p, C.c_int, C.c_uint64]
+        _flib.orcf_destroy.argtypes = [C.c_void_p]
+        _flib.orcf_time_mult_relin_rescale.restype = C.c_double
+    return _flib
+
+
+class FastOracle:
+    """CKKS mult / relin / rescale / rotate of the optimised CPU baseline (same array conventions as Oracle)"""
+
+    def __init__(self, params):
+        self.p, self.N = params, params.N
+        q = np.array(params.q, dtype=np.uint64)
+        pp = np.array(params.p, dtype=np.uint64)
+        self.h = fast_lib().orcf_create(params.scheme, params.logN, P(q), len(q), P(pp), len(pp), params.t)
+        if not self.h:
+            raise RuntimeError("orcf_create failed for " + params.name)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            fast_lib().orcf_destroy(C.c_void_p(self.h))
+            self.h = None
+
+    @property
+    def hp(self):
+        return C.c_void_p(self.h)
+
+    def ntt(self, midx, a, inverse=False):
+        out = np.ascontiguousarray(a, dtype=np.uint64).copy()
+        fast_lib().orcf_ntt(self.hp, midx, P(out), 1 if inverse else 0)
+        return out
+
+    def mult_relin(self, a, b, rlk, rescale=False):
+        a = np.ascontiguousarray(a, dtype=np.uint64)
+        b = np.ascontiguousarray(b, dtype=np.uint64)
+        l = a.shape[1]
+        key_level = rlk.shape[2] - self.p.k - 1
+        o = np.zeros((2, l - 1 if rescale else l, self.N), dtype=np.uint64)
+        fn = fast_lib().orcf_ckks_mult_relin_rescale if rescale else fast_lib().orcf_ckks_mult_relin
+        fn(self.hp, l - 1, P(a), P(b), P(rlk), key_level, P(o))
+        return o
+
+    def time_mult_relin_rescale(self, a, b, rlk, reps):
+        l = a.shape[1]
+        key_level = rlk.shape[2] - self.p.k - 1
+        o = np.zeros((2, l - 1, self.N), dtype=np.uint64)
+        return fast_lib().orcf_time_mult_relin_rescale(self.hp, l - 1, P(a), P(b), P(rlk), key_level, P(o), reps)
+
+    def rotate(self, ct, glk, gal):
+        ct = np.ascontiguousarray(ct, dtype=np.uint64)
+        l = ct.shape[1]
+        key_level = glk.shape[2] - self.p.k - 1
+        o = np.zeros((2, l, self.N), dtype=np.uint64)
+        fast_lib().orcf_ckks_rotate(self.hp, l - 1, P(ct), P(glk), key_level, C.c_uint64(gal), P(o))
+        return o
 
 
 # ---------------------------------------------------------------------------------------------

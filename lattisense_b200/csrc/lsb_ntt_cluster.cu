@@ -13,12 +13,18 @@
 // Lattigo ring.NTT / ring.InvNTT ordering).
 #include <cooperative_groups.h>
 #include <cstdlib>
+#include <map>
+#include <mutex>
 #include <type_traits>
 
 #include "lsb_kernels.h"
 #include "lsb_ntt_core.h"
 #include "lsb_ntt_cluster_core.h"
+#include "lsb_ntt_persist_core.h"
 
+#ifndef LSB_CL_RMAJOR
+#define LSB_CL_RMAJOR 0
+#endif
 #ifndef LSB_CL_MINB
 #define LSB_CL_MINB 4
 #endif
@@ -74,6 +80,11 @@ struct NttClArgs {
     // other ranks' GPUs, written over NVLink while the transform's remaining groups are still being computed
     int npeer;
     u64* peer[kMaxPeers];
+    // persistent kernel (k_ntt_persist): limbs are visited row-major (work item i -> row i / batch, item i % batch) so
+    // that a cluster stays on one modulus; twp / twp_d are the PLAIN bit-reversed tables it stages into shared memory
+    int batch;
+    const Tw* twp;
+    const TwD* twp_d;
 };
 
 template <int I, int NR, class F>
@@ -98,7 +109,13 @@ __device__ __forceinline__ void ntt_cluster_body(const NttClArgs& a, u64* sm) {
     const int tid = threadIdx.x;
     const int rank = CL > 1 ? (int)(blockIdx.x % CL) : 0;
     const int row = blockIdx.x / CL;
+#if LSB_CL_RMAJOR
+    // modulus-major order: consecutive clusters transform the same limb of consecutive batch items, so the CTAs that
+    // share an SM read the same twiddles (L1 hits instead of L2 round trips)
+    const int r = row / a.batch, b = row - r * a.batch;
+#else
     const int b = row / a.map.n, r = row - b * a.map.n;
+#endif
     const u64* src = a.in.at(b) + (size_t)a.map.in_slot[r] * N;
     u64* dst = a.out.at(b) + (size_t)a.map.out_slot[r] * N;
     const int mod = a.map.mod[r];
@@ -227,6 +244,390 @@ __global__ void __launch_bounds__(ClusterCfg<LOGN>::NT, ClusterCfg<LOGN>::MINB) 
     ntt_cluster_body<LOGN, INV, P, FIN, PEERS>(a, sm);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Persistent variant (N <= 2^14; OPT-IN with LSB_NTT_PERSIST=1, measured SLOWER than one cluster per limb on B200:
+// 2.33 vs 2.75 TB/s forward, 2.15 vs 2.49 inverse at N = 2^14 -- profiles/r02_ntt_persist_experiment.txt; it removes
+// every long-scoreboard stall but its 48 KiB of shared memory per CTA leave 16 warps per SM instead of 32, and the
+// FP64 dependency latency then shows as stall_wait / short_scoreboard): a fixed set of clusters, as many as the device holds at once, each walking
+// a contiguous range of the launch's limbs in row-major order (all limbs of one modulus before the next).  What this
+// buys over one cluster per limb (ncu of k_ntt_cluster, profiles/r02_ntt14_base_stalls.txt: a third of all warp
+// stalls are long-scoreboard waits, ~45 % of them on twiddle loads from L2 and ~35 % on the transform's own input):
+//   * the twiddles of the blocks a CTA owns (2^LS - 1 per block; as many bytes as the data tile itself) are staged
+//     in SHARED memory once per modulus and re-used for every limb of that modulus -- the local rounds issue no
+//     global load at all;
+//   * the next limb's input is loaded into registers right after the current limb's cross round has been handed to
+//     the peers, i.e. a whole limb ahead of its use: its HBM latency hides behind the cluster barrier and the local
+//     rounds.  Occupancy is set by shared memory (48 KiB per CTA at N = 2^14: 4 CTAs per SM), so the 32 extra
+//     registers are free;
+//   * the cluster barrier is split: "my tile may be overwritten" is signalled (arrive) after the output copy and
+//     awaited only after the next limb's cross-round butterflies, "scatter done" is signalled before the prefetch is
+//     issued and awaited after it.
+// Arithmetic, indexing and data layout are those of k_ntt_cluster (same round code), so the limbs are identical.
+template <int LOGN>
+struct PersistCfg {
+    typedef ClusterCfg<LOGN> C;
+    static constexpr int NT = LOGN == 14 ? 128 : 256;
+    static constexpr int MINB = LOGN == 14 ? 4 : 2;
+    static constexpr int LRL = cluster_last_lr(LOGN);
+    static constexpr int S1L = C::LS - LRL;           // local first stage of the contiguous last round
+    static constexpr int GPT = C::G0 / NT;            // cross-round groups per thread
+    static constexpr size_t SMEM = (size_t)C::TILE * 8 + (size_t)C::NB * C::BS * 16 + 16 * 16 + 16;  // + mbarrier
+    static_assert(C::G0 % NT == 0, "cross-round groups must divide evenly over the CTA");
+};
+
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+// "I no longer READ shared memory of this phase": no data is published, so no release fence (which would also wait for
+// the output copy's global stores to drain -- 10 % of all stall samples in profiles/r02_ntt14_persist_v1_stalls.txt)
+__device__ __forceinline__ void cluster_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory"); }
+
+// ---- asynchronous scatter (forward cross round): st.async writes one word into a peer's tile and counts its bytes on
+// the PEER's mbarrier, so the receiver just waits for TILE * 8 bytes to land -- no release fence after the remote
+// stores (ERRBAR: 9 % of stall samples) and no cluster-wide barrier for this phase
+#ifndef LSB_PERSIST_STASYNC
+#define LSB_PERSIST_STASYNC 1
+#endif
+__device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ u32 mapa_u32(u32 local, int rank) {
+    u32 r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void st_async_u64(u32 remote_addr, u64 v, u32 remote_mbar) {
+    asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.b64 [%0], %1, [%2];" ::"r"(remote_addr), "l"(v), "r"(remote_mbar)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_init(u32 mbar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(u32 mbar, u32 bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(u32 mbar, u32 parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "LSB_MBAR_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra LSB_MBAR_DONE;\n"
+        "bra LSB_MBAR_WAIT;\n"
+        "LSB_MBAR_DONE:\n"
+        "}\n" ::"r"(mbar),
+        "r"(parity)
+        : "memory");
+}
+
+template <class P>
+__device__ __forceinline__ const typename P::TW* twp_of(const NttClArgs& a, int mod, int N) {
+    if constexpr (std::is_same<P, ArithF64>::value) return a.twp_d + (size_t)mod * N;
+    else return a.twp + (size_t)mod * N;
+}
+
+template <int LOGN, bool INV, class P, bool FIN>
+__global__ void __launch_bounds__(PersistCfg<LOGN>::NT, PersistCfg<LOGN>::MINB) k_ntt_persist(const __grid_constant__ NttClArgs a) {
+    typedef ClusterCfg<LOGN> C;
+    typedef PersistCfg<LOGN> PC;
+    typedef typename P::TW TW;
+    constexpr int N = C::N, CL = C::CL, BS = C::BS, NB = C::NB, TILE = C::TILE, NT = PC::NT, GPT = PC::GPT;
+    constexpr Plan PL = make_plan(C::LS, 0);
+    extern __shared__ __align__(1024) u64 sm[];
+    TW* tws = reinterpret_cast<TW*>(sm + TILE);  // [NB][BS] local tables (lsb_ntt_persist_core.h)
+    TW* twx = tws + NB * BS;                     // [16] cross-round twiddles (entries 1..15 of the plain table)
+    const int tid = threadIdx.x;
+    const int rank = CL > 1 ? (int)(blockIdx.x % CL) : 0;
+    const int ncl = (int)(gridDim.x / CL), cid = (int)(blockIdx.x / CL);
+    const int per = (a.total_rows + ncl - 1) / ncl;
+    const int i0 = cid * per, i1 = min(a.total_rows, i0 + per);
+    cg::cluster_group cluster = cg::this_cluster();
+    u64* peer[CL];
+#pragma unroll
+    for (int c = 0; c < CL; c++) peer[c] = CL > 1 ? cluster.map_shared_rank(sm, c) : sm;
+    constexpr bool ASYNC = LSB_PERSIST_STASYNC && CL > 1 && !INV;
+    const u32 mbar = smem_u32(twx + 16);
+    u32 phase = 0;
+    if (ASYNC && tid == 0) mbar_init(mbar, 1);
+    if (CL > 1) cluster.sync();  // every CTA of the cluster is resident (and its mbarrier initialised) before it is addressed
+    if (i0 >= i1) return;        // (uniform over the cluster)
+
+    int cur_mod = -1;
+    ModCtx m{};
+    auto row_of = [&](int i, int& b, int& r) {
+        r = i / a.batch;
+        b = i - r * a.batch;
+    };
+    auto stage_twiddles = [&](int mod) {
+        const TW* plain = twp_of<P>(a, mod, N);
+        for (int idx = tid; idx < NB * BS; idx += NT) {
+            const int st = idx / BS, li = idx - st * BS;
+            if (li) tws[idx] = plain[persist_tw_src((u32)li, rank * NB + st, C::LS, PC::LRL)];
+        }
+        if (tid < 16) twx[tid] = plain[tid];
+        const ModConst& mc = a.mods[mod];
+        m.q = mc.q;
+        m.q2 = mc.q << 1;
+        m.qinv64 = mc.qinv64;
+        m.qd = mc.qd;
+        m.qinvd = mc.qinvd;
+        m.lazy = mc.q < kLazyLimit;
+        m.recentre = mc.f64_recentre != 0;
+        __syncthreads();
+    };
+
+    if (!INV) {
+        u64 xn[GPT][16];  // next limb's cross-round input, raw residues
+        auto prefetch = [&](int i) {
+            int b, r;
+            row_of(i, b, r);
+            const u64* src = a.in.at(b) + (size_t)a.map.in_slot[r] * N;
+#pragma unroll
+            for (int j = 0; j < GPT; j++) {
+                const int g = rank * C::G0 + tid + j * NT;
+#pragma unroll
+                for (int k = 0; k < 16; k++) xn[j][k] = src[g + k * BS];
+            }
+        };
+        prefetch(i0);
+        for (int i = i0; i < i1; i++) {
+            int b, r;
+            row_of(i, b, r);
+            const int mod = a.map.mod[r];
+            if (mod != cur_mod) {
+                stage_twiddles(mod);
+                cur_mod = mod;
+            }
+            // ---- cross round on the prefetched words g + k*BS ----
+            typename P::V x[GPT][16];
+#pragma unroll
+            for (int j = 0; j < GPT; j++) {
+#pragma unroll
+                for (int k = 0; k < 16; k++) x[j][k] = P::from_raw(xn[j][k]);
+                fwd_stages<P, 4>(x[j], twx, 1u, m);
+            }
+            if (CL > 1 && i > i0) cluster_wait();  // every CTA of the cluster is done with the previous limb's tile
+            else if (CL == 1) __syncthreads();
+            if constexpr (ASYNC) {
+                if (tid == 0) mbar_expect_tx(mbar, TILE * 8);
+                const u32 tile0 = smem_u32(sm);
+#pragma unroll
+                for (int j = 0; j < GPT; j++) {
+                    const int g = rank * C::G0 + tid + j * NT;
+                    const u32 off = (u32)swz(g) * 8;
+#pragma unroll
+                    for (int c = 0; c < CL; c++) {
+                        const u32 rt = mapa_u32(tile0, c), rm = mapa_u32(mbar, c);
+#pragma unroll
+                        for (int kk = 0; kk < NB; kk++) st_async_u64(rt + (u32)(kk * BS) * 8 + off, P::to_bits(x[j][c * NB + kk]), rm);
+                    }
+                }
+                if (i + 1 < i1) prefetch(i + 1);
+                mbar_wait(mbar, phase);
+                phase ^= 1;
+            } else {
+#pragma unroll
+                for (int j = 0; j < GPT; j++) {
+                    const int g = rank * C::G0 + tid + j * NT;
+#pragma unroll
+                    for (int k = 0; k < 16; k++) peer[k / NB][(k % NB) * BS + swz(g)] = P::to_bits(x[j][k]);
+                }
+                if (CL > 1) cluster_arrive();
+                if (i + 1 < i1) prefetch(i + 1);
+                if (CL > 1) cluster_wait();
+                else __syncthreads();
+            }
+            // ---- local rounds on the NB blocks this CTA owns, twiddles from shared memory ----
+            static_for_cl<0, PL.nrounds>([&](auto ic) {
+                constexpr int ir = decltype(ic)::value;
+                constexpr int lr = PL.rounds[ir].lr;
+                constexpr int loggc = plan_loggc(PL, ir);
+                constexpr bool last = ir == PL.nrounds - 1;
+                constexpr int GPB = BS >> lr;
+#pragma unroll
+                for (int gg = tid; gg < NB * GPB; gg += NT) {
+                    const int st = gg / GPB, g = gg - st * GPB;
+                    local_round<P, lr, false, false, last, (last ? PC::S1L : -1)>(sm + st * BS, tws + st * BS, g, loggc,
+                                                                                   PL.rounds[ir].v, 1u, m, nullptr, nullptr);
+                }
+                __syncthreads();
+            });
+            if constexpr (!FIN) {
+                u64* out = a.out.at(b) + (size_t)a.map.out_slot[r] * N + (size_t)rank * TILE;
+                for (int c = tid; c < TILE / 2; c += NT) reinterpret_cast<W2*>(out)[c] = *reinterpret_cast<const W2*>(&sm[swz(2 * c)]);
+            } else {
+                const int f = a.map.out_slot[r];
+                const FinishMap& fm = *a.fm;
+                const Tw cmul = fm.c[f];
+                const u64 q = m.q;
+                const size_t off = (size_t)rank * (TILE / 2);
+                const W2* pa = reinterpret_cast<const W2*>(a.fa.at(b) + (size_t)fm.a_slot[f] * N) + off;
+                const bool add = a.has_add && fm.add_slot[f] != 0xFF;
+                const W2* pz = add ? reinterpret_cast<const W2*>(a.fadd.at(b) + (size_t)fm.add_slot[f] * N) + off : nullptr;
+                W2* po = reinterpret_cast<W2*>(a.fout.at(b) + (size_t)fm.out_slot[f] * N) + off;
+                for (int c = tid; c < TILE / 2; c += NT) {
+                    const W2 y = *reinterpret_cast<const W2*>(&sm[swz(2 * c)]);
+                    const W2 xa = pa[c];
+                    W2 o;
+                    o.a = mul_shoup(submod(xa.a, y.a, q), cmul, q);
+                    o.b = mul_shoup(submod(xa.b, y.b, q), cmul, q);
+                    if (add) {
+                        const W2 z = pz[c];
+                        o.a = addmod(o.a, z.a, q);
+                        o.b = addmod(o.b, z.b, q);
+                    }
+                    po[c] = o;
+                }
+            }
+            if (CL > 1 && i + 1 < i1) cluster_arrive_relaxed();  // this thread no longer reads the tile
+        }
+    } else {
+        constexpr int LRL = PC::LRL, GPBL = BS >> LRL, RL = 1 << LRL;
+        constexpr int GPTL = (NB * GPBL) / NT;  // first-inverse-round groups per thread
+        static_assert((NB * GPBL) % NT == 0, "first inverse round must divide evenly over the CTA");
+        W2 xn[GPTL][RL / 2];
+        auto prefetch = [&](int i) {
+            int b, r;
+            row_of(i, b, r);
+            const u64* src = a.in.at(b) + (size_t)a.map.in_slot[r] * N + (size_t)rank * TILE;
+#pragma unroll
+            for (int j = 0; j < GPTL; j++) {
+                const int gg = tid + j * NT;
+                const W2* p = reinterpret_cast<const W2*>(src + (size_t)gg * RL);  // st * BS + g * RL == gg * RL
+#pragma unroll
+                for (int k = 0; k < RL / 2; k++) xn[j][k] = p[k];
+            }
+        };
+        prefetch(i0);
+        for (int i = i0; i < i1; i++) {
+            int b, r;
+            row_of(i, b, r);
+            const int mod = a.map.mod[r];
+            if (mod != cur_mod) {
+                stage_twiddles(mod);
+                cur_mod = mod;
+            }
+            u64* dst = a.out.at(b) + (size_t)a.map.out_slot[r] * N;
+            // ---- first inverse round (contiguous) from the prefetched registers into the tile ----
+            if (CL > 1 && i > i0) cluster_wait();  // the peers have gathered the previous limb out of this tile
+#pragma unroll
+            for (int j = 0; j < GPTL; j++) {
+                const int gg = tid + j * NT;
+                const int st = gg / GPBL, g = gg - st * GPBL;
+                typename P::V x[RL];
+#pragma unroll
+                for (int k = 0; k < RL / 2; k++) {
+                    x[2 * k] = P::from_raw(xn[j][k].a);
+                    x[2 * k + 1] = P::from_raw(xn[j][k].b);
+                }
+                inv_stages<P, LRL, false, PC::S1L>(x, tws + st * BS, ((u32)1 << PC::S1L) + (u32)g, m, TW{}, TW{});
+                u64* smt = sm + st * BS;
+#pragma unroll
+                for (int k = 0; k < RL; k += 2) {
+                    W2 pr;
+                    pr.a = P::to_bits(x[k]);
+                    pr.b = P::to_bits(x[k + 1]);
+                    *reinterpret_cast<W2*>(&smt[swz(g * RL + k)]) = pr;
+                }
+            }
+            __syncthreads();
+            if (i + 1 < i1) prefetch(i + 1);
+            static_for_cl<1, PL.nrounds>([&](auto ic) {
+                constexpr int ir = PL.nrounds - 1 - decltype(ic)::value;
+                constexpr int lr = PL.rounds[ir].lr;
+                constexpr int loggc = plan_loggc(PL, ir);
+                constexpr int GPB = BS >> lr;
+#pragma unroll
+                for (int gg = tid; gg < NB * GPB; gg += NT) {
+                    const int st = gg / GPB, g = gg - st * GPB;
+                    local_round<P, lr, true, false, false, -1>(sm + st * BS, tws + st * BS, g, loggc, PL.rounds[ir].v, 1u, m,
+                                                               nullptr, nullptr);
+                }
+                __syncthreads();
+            });
+            if (CL > 1) {
+                cluster_arrive();
+                cluster_wait();
+            }
+            TW ninv, w_ninv;
+            {
+                const ModConst& mc = a.mods[mod];
+                if constexpr (std::is_same<P, ArithF64>::value) {
+                    ninv = mc.ninv_d;
+                    w_ninv = mc.w_ninv_d;
+                } else {
+                    ninv = mc.ninv;
+                    w_ninv = mc.w_ninv;
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < GPT; j++) {
+                const int g = rank * C::G0 + tid + j * NT;
+                typename P::V x[16];
+#pragma unroll
+                for (int k = 0; k < 16; k++) x[k] = P::from_bits(peer[k / NB][(k % NB) * BS + swz(g)]);
+                inv_stages<P, 4, true>(x, twx, 1u, m, ninv, w_ninv);
+#pragma unroll
+                for (int k = 0; k < 16; k++) dst[g + k * BS] = P::inv_canonical(x[k], m);
+            }
+            if (CL > 1 && i + 1 < i1) cluster_arrive_relaxed();  // done reading the peers' tiles
+            else if (CL == 1) __syncthreads();
+        }
+        if (CL > 1) cluster.sync();  // no CTA leaves while a peer may still read its shared memory
+    }
+}
+
+template <int LOGN, class K>
+static void launch_persist_k(K kernel, NttClArgs a, int sm_count, cudaStream_t s) {
+    typedef ClusterCfg<LOGN> C;
+    typedef PersistCfg<LOGN> PC;
+    // per kernel (K is the same function-pointer type for every instantiation, so key by address)
+    static std::mutex mu;
+    static std::map<const void*, int> cache;
+    std::lock_guard<std::mutex> lock(mu);
+    int& max_clusters = cache[(const void*)kernel];
+    cudaLaunchConfig_t cfg = {};
+    cfg.blockDim = dim3(PC::NT, 1, 1);
+    cfg.dynamicSmemBytes = PC::SMEM;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = C::CL;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    if (max_clusters == 0) {
+        LSB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PC::SMEM));
+        LSB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        cfg.gridDim = dim3((unsigned)(sm_count * PC::MINB), 1, 1);
+        int n = 0;
+        LSB_CUDA(cudaOccupancyMaxActiveClusters(&n, kernel, &cfg));
+        static const int cap = [] {
+            const char* e = getenv("LSB_NTT_PERSIST_CLUSTERS");
+            return e ? atoi(e) : 0;
+        }();
+        max_clusters = std::max(1, cap > 0 ? std::min(cap, n) : n);
+    }
+    const int ncl = std::min(a.total_rows, max_clusters);
+    cfg.gridDim = dim3((unsigned)(ncl * C::CL), 1, 1);
+    LSB_CUDA(cudaLaunchKernelEx(&cfg, kernel, a));
+}
+
+template <int LOGN>
+static void launch_persist_n(const NttClArgs& a, bool inverse, bool f64, int sm_count, cudaStream_t s) {
+    if (a.fm) {
+        if (f64) launch_persist_k<LOGN>(k_ntt_persist<LOGN, false, ArithF64, true>, a, sm_count, s);
+        else launch_persist_k<LOGN>(k_ntt_persist<LOGN, false, ArithU64, true>, a, sm_count, s);
+        return;
+    }
+    if (f64) {
+        if (inverse) launch_persist_k<LOGN>(k_ntt_persist<LOGN, true, ArithF64, false>, a, sm_count, s);
+        else launch_persist_k<LOGN>(k_ntt_persist<LOGN, false, ArithF64, false>, a, sm_count, s);
+    } else {
+        if (inverse) launch_persist_k<LOGN>(k_ntt_persist<LOGN, true, ArithU64, false>, a, sm_count, s);
+        else launch_persist_k<LOGN>(k_ntt_persist<LOGN, false, ArithU64, false>, a, sm_count, s);
+    }
+}
+
 template <int LOGN, class K>
 static void launch_cluster_k(K kernel, const NttClArgs& a, cudaStream_t s) {
     typedef ClusterCfg<LOGN> C;
@@ -309,7 +710,22 @@ void launch_ntt_cluster(const DeviceTables& dt, BatchPtr in, BatchPtr out, const
         }
         a.npeer = npeer;
         for (int pr = 0; pr < npeer; pr++) a.peer[pr] = peers[pr];
+        a.batch = batch;
+        a.twp = inverse ? dt.tw_inv : dt.tw_fwd;
+        a.twp_d = inverse ? dt.tw_inv_d : dt.tw_fwd_d;
         ProfScope _ps(dt.prof, inverse ? PK_NTT_INV : PK_NTT_FWD, s, 16.0 * dt.N * a.total_rows, 1);
+        static const bool persist = [] {  // LSB_NTT_PERSIST=1: persistent clusters (k_ntt_persist) for N <= 2^14
+            const char* e = getenv("LSB_NTT_PERSIST");
+            return e && atoi(e) != 0;
+        }();
+        if (persist && npeer == 0 && dt.logN <= 14) {
+            switch (dt.logN) {
+                case 12: launch_persist_n<12>(a, inverse, f == 1, dt.sm_count, s); break;
+                case 13: launch_persist_n<13>(a, inverse, f == 1, dt.sm_count, s); break;
+                default: launch_persist_n<14>(a, inverse, f == 1, dt.sm_count, s); break;
+            }
+            continue;
+        }
         switch (dt.logN) {
             case 12: launch_cluster_n<12>(a, inverse, f == 1, s); break;
             case 13: launch_cluster_n<13>(a, inverse, f == 1, s); break;

@@ -30,6 +30,7 @@ def emul():
     i32p = C.POINTER(C.c_int)
     lib.emul_ntt.argtypes = [C.c_int, C.c_uint64, u64p, C.c_int, C.c_int]
     lib.emul_ntt_cluster.argtypes = [C.c_int, C.c_uint64, u64p, C.c_int, C.c_int]
+    lib.emul_ntt_persist.argtypes = [C.c_int, C.c_uint64, u64p, C.c_int, C.c_int]
     lib.emul_basis_extend.argtypes = [C.c_int, u64p, C.c_int, i32p, C.c_int, i32p, C.c_int, C.c_int, u64p, u64p]
     lib.emul_reduce_wide.restype = C.c_uint64
     lib.emul_reduce_wide.argtypes = [C.c_uint64] * 3

@@ -7,6 +7,7 @@
 #include "../../lattisense_b200/csrc/lsb_tables.h"
 #include "../../lattisense_b200/csrc/lsb_elem_core.h"
 #include "../../lattisense_b200/csrc/lsb_ntt_cluster_core.h"
+#include "../../lattisense_b200/csrc/lsb_ntt_persist_core.h"
 
 using namespace lsb;
 
@@ -182,7 +183,107 @@ static void cluster_ntt(int logN, const typename P::TW* tw, const ModConst& mc, 
     }
 }
 
+
+// mirrors k_ntt_persist (lsb_ntt_cluster.cu): the same rounds with each block's twiddles taken from its own local
+// table (built from the PLAIN table through persist_tw_src, indexed with twbase = 1 and the local tail-SoA stage)
+template <class P, int LOGN, bool INV>
+static void persist_rounds(u64* sm, const typename P::TW* tws, const ModCtx& m, u64* data) {
+    constexpr int N = 1 << LOGN, BS = N / 16, LS = LOGN - 4;
+    constexpr Plan PL = make_plan(LS, 0);
+    constexpr int LRL = cluster_last_lr(LOGN), S1L = LS - LRL;
+    for (int j = 0; j < PL.nrounds; j++) {
+        const int i = INV ? PL.nrounds - 1 - j : j;
+        const int lr = PL.rounds[i].lr, loggc = plan_loggc(PL, i), v = PL.rounds[i].v;
+        const bool last = i == PL.nrounds - 1;
+        for (int blk = 0; blk < 16; blk++)
+            for (int g = 0; g < (BS >> lr); g++) {
+                u64* smt = sm + blk * BS;
+                const typename P::TW* tw = tws + (size_t)blk * BS;
+                u64* gio = data + blk * BS;
+                if (lr == 4 && !last) local_round<P, 4, INV, false, false, -1>(smt, tw, g, loggc, v, 1u, m, gio, gio);
+                else if (lr == 3 && !last) local_round<P, 3, INV, false, false, -1>(smt, tw, g, loggc, v, 1u, m, gio, gio);
+                else if (lr == 4) local_round<P, 4, INV, INV, !INV, S1L>(smt, tw, g, loggc, v, 1u, m, gio, nullptr);
+                else if (lr == 3) local_round<P, 3, INV, INV, !INV, S1L>(smt, tw, g, loggc, v, 1u, m, gio, nullptr);
+                else throw std::runtime_error("emul: unhandled persistent round");
+            }
+    }
+}
+template <class P, int LOGN>
+static void persist_ntt_n(const typename P::TW* plain, const ModConst& mc, typename P::TW ninv, typename P::TW w_ninv, u64* data,
+                          bool inverse) {
+    constexpr int N = 1 << LOGN, BS = N / 16, LS = LOGN - 4;
+    constexpr Plan PL = make_plan(LS, 0);
+    constexpr int LRL = cluster_last_lr(LOGN), S1L = LS - LRL;
+    ModCtx m;
+    m.q = mc.q;
+    m.q2 = mc.q << 1;
+    m.qinv64 = mc.qinv64;
+    m.qd = mc.qd;
+    m.qinvd = mc.qinvd;
+    m.lazy = mc.q < kLazyLimit;
+    m.recentre = mc.f64_recentre != 0;
+    std::vector<typename P::TW> tws((size_t)16 * BS), twx(16);
+    for (int blk = 0; blk < 16; blk++)
+        for (int li = 1; li < BS; li++) tws[(size_t)blk * BS + li] = plain[persist_tw_src((u32)li, blk, LS, LRL)];
+    for (int i = 0; i < 16; i++) twx[i] = plain[i];
+    std::vector<u64> sm(N);
+    if (!inverse) {
+        for (int g = 0; g < BS; g++) {
+            typename P::V x[16];
+            for (int k = 0; k < 16; k++) x[k] = P::from_raw(data[g + k * BS]);
+            fwd_stages<P, 4>(x, twx.data(), 1u, m);
+            for (int k = 0; k < 16; k++) sm[k * BS + swz(g)] = P::to_bits(x[k]);
+        }
+        persist_rounds<P, LOGN, false>(sm.data(), tws.data(), m, data);
+        for (int c = 0; c < N / 2; c++) {
+            const int blk = (2 * c) / BS, u = (2 * c) % BS;
+            data[2 * c] = sm[blk * BS + swz(u)];
+            data[2 * c + 1] = sm[blk * BS + swz(u) + 1];
+        }
+    } else {
+        persist_rounds<P, LOGN, true>(sm.data(), tws.data(), m, data);
+        for (int g = 0; g < BS; g++) {
+            typename P::V x[16];
+            for (int k = 0; k < 16; k++) x[k] = P::from_bits(sm[k * BS + swz(g)]);
+            inv_stages<P, 4, true>(x, twx.data(), 1u, m, ninv, w_ninv);
+            for (int k = 0; k < 16; k++) data[g + k * BS] = P::inv_canonical(x[k], m);
+        }
+    }
+}
+template <class P>
+static void persist_ntt(int logN, const typename P::TW* plain, const ModConst& mc, typename P::TW ninv, typename P::TW w_ninv,
+                        u64* data, bool inverse) {
+    switch (logN) {
+        case 12: return persist_ntt_n<P, 12>(plain, mc, ninv, w_ninv, data, inverse);
+        case 13: return persist_ntt_n<P, 13>(plain, mc, ninv, w_ninv, data, inverse);
+        case 14: return persist_ntt_n<P, 14>(plain, mc, ninv, w_ninv, data, inverse);
+        case 15: return persist_ntt_n<P, 15>(plain, mc, ninv, w_ninv, data, inverse);
+        case 16: return persist_ntt_n<P, 16>(plain, mc, ninv, w_ninv, data, inverse);
+        default: throw std::runtime_error("emul: unsupported ring degree");
+    }
+}
+
 extern "C" {
+
+int emul_ntt_persist(int logN, u64 q, u64* data, int inverse, int f64) {
+    try {
+        const int N = 1 << logN;
+        std::vector<Tw> f(N), iv(N);
+        std::vector<TwD> fd(N), ivd(N);
+        ModConst mc;
+        build_ntt_tables(q, logN, f.data(), iv.data(), &mc, fd.data(), ivd.data());
+        if (f64) {
+            if (!mc.f64_ok) return 2;
+            persist_ntt<ArithF64>(logN, inverse ? ivd.data() : fd.data(), mc, mc.ninv_d, mc.w_ninv_d, data, inverse != 0);
+        } else {
+            persist_ntt<ArithU64>(logN, inverse ? iv.data() : f.data(), mc, mc.ninv, mc.w_ninv, data, inverse != 0);
+        }
+        return 0;
+    } catch (const std::exception& e) {
+        fprintf(stderr, "emul_ntt_persist: %s\n", e.what());
+        return 1;
+    }
+}
 
 // f64: 1 = FP64 butterfly policy (returns 2 if the prime does not qualify), 0 = 64-bit Shoup/Harvey policy
 int emul_ntt_cluster(int logN, u64 q, u64* data, int inverse, int f64) {

@@ -119,9 +119,12 @@ def test_reduce_wide_up_to_its_bound(emul):
 
 @pytest.mark.parametrize("params", [R.CKKS_N12, R.CKKS_N13, R.CKKS_N14, R.BFV_N13, R.CKKS_BTP_N15, R.CKKS_BTP_N16],
                          ids=lambda p: p.name)
-def test_cluster_ntt_both_policies_match_oracle(emul, params):
-    """k_ntt_cluster's round code on the CPU: the FP64 policy (eligible primes) and the 64-bit policy give the
-    oracle's limbs bit for bit, forward and inverse, including extreme residues."""
+@pytest.mark.parametrize("kernel", ["emul_ntt_cluster", "emul_ntt_persist"])
+def test_cluster_ntt_both_policies_match_oracle(emul, params, kernel):
+    """k_ntt_cluster's / k_ntt_persist's round code on the CPU (the persistent kernel reads each block's twiddles from
+    its own shared-memory table, lsb_ntt_persist_core.h): the FP64 policy (eligible primes) and the 64-bit policy give
+    the oracle's limbs bit for bit, forward and inverse, including extreme residues."""
+    run = getattr(emul, kernel)
     o = R.Oracle(params)
     rng = np.random.default_rng(5)
     n_f64 = 0
@@ -134,14 +137,14 @@ def test_cluster_ntt_both_policies_match_oracle(emul, params):
         for f64 in (0, 1):
             for vec in (a, worst):
                 fwd = vec.copy()
-                rc = emul.emul_ntt_cluster(params.logN, q, R.P(fwd), 0, f64)
+                rc = run(params.logN, q, R.P(fwd), 0, f64)
                 if rc == 2:
                     assert f64 == 1 and q * (params.logN + 1) >= 2 ** 51
                     break
                 assert rc == 0
                 assert np.array_equal(fwd, o.ntt(mid, vec))
                 inv = vec.copy()
-                assert emul.emul_ntt_cluster(params.logN, q, R.P(inv), 1, f64) == 0
+                assert run(params.logN, q, R.P(inv), 1, f64) == 0
                 assert np.array_equal(inv, o.ntt(mid, vec, inverse=True))
             else:
                 n_f64 += f64

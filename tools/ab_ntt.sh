@@ -1,9 +1,18 @@
 #!/bin/bash
 # rebuild lsb_ntt_cluster.cu with different -D flags on the GPU box and time the NTT (development aid)
+# usage: ab_ntt.sh "ENV=.. -Dflags" ...   (leading VAR=value words are exported to the timing runs)
 cd lattisense_b200/csrc
-for flags in "$@"; do
-  echo "== $flags"
+for spec in "$@"; do
+  echo "== $spec"
+  envs=""; flags=""
+  for w in $spec; do case "$w" in -D*) flags="$flags $w";; *) envs="$envs $w";; esac; done
   rm -f ../_build/lsb_ntt_cluster.o
   make -s NVFLAGS_EXTRA="$flags" >/dev/null 2>&1 || { echo build failed; continue; }
-  (cd ../..; python tools/prof_ntt.py 14 8192 20 t; python tools/prof_ntt.py 16 2048 20 t; PROF_MOD0=0 PROF_NMOD=1 python tools/prof_ntt.py 16 2048 20 t) 2>&1 | grep -v "^ok"
+  (cd ../..; env $envs timeout 120 python tools/prof_ntt.py 14 8192 20 t; env $envs timeout 200 python bench.py --no-cpu --no-api --no-secondary --steps 5 2>&1 | python -c "
+import sys,json
+for line in sys.stdin:
+    try: d=json.loads(line)
+    except Exception: continue
+    r=d['roofline']; print('step %.3f ms  ntt_instep %.0f GB/s frac %.3f standalone %.0f' % (d['ms_per_step'], r['achieved'], r['frac'], r['standalone_ntt_gbs'])); print(d['kernel_ms_per_step'])
+") 2>&1 | grep -v "^ok"
 done

@@ -104,8 +104,25 @@ Context::Context(int device_, int scheme_, int logN_, const u64* q, int nq_, con
     ws0_.reset(new Workspace(device));
 }
 
+Context::SidePipe& Context::side_pipe() {
+    std::lock_guard<std::mutex> lk(mu_);
+    if (!side_.stream) {
+        LSB_CUDA(cudaSetDevice(device));
+        LSB_CUDA(cudaStreamCreateWithFlags(&side_.stream, cudaStreamNonBlocking));
+        LSB_CUDA(cudaEventCreateWithFlags(&side_.fork, cudaEventDisableTiming));
+        LSB_CUDA(cudaEventCreateWithFlags(&side_.join, cudaEventDisableTiming));
+    }
+    return side_;
+}
+
 Context::~Context() {
     cudaSetDevice(device);
+    if (side_.stream) {
+        cudaStreamSynchronize(side_.stream);
+        cudaStreamDestroy(side_.stream);
+        cudaEventDestroy(side_.fork);
+        cudaEventDestroy(side_.join);
+    }
     ws0_.reset();
     for (void* p : owned_) cudaFree(p);
 }

@@ -66,6 +66,12 @@ struct Context {
     const ScaleUpConsts* bfv_scale_up_consts(int level);
 
     Workspace& default_workspace() { return *ws0_; }
+    // side stream + fork/join events of the two-stream batch pipeline (lsb_ops.cu: mult_relin_chain); created on first use
+    struct SidePipe {
+        cudaStream_t stream = nullptr;
+        cudaEvent_t fork = nullptr, join = nullptr;
+    };
+    SidePipe& side_pipe();
     // limb-sharded key-switch tables (lsb_shard.cu), cached per (level, world, rank)
     const ShardPlan& shard_plan(int level, int world, int rank);
     const void* upload_raw(const void* host, size_t bytes) {
@@ -85,6 +91,7 @@ private:
     std::unordered_map<const void*, std::vector<BexMeta>> bex_meta_;
     const void* upload_jobs(const std::vector<BexJob>& jobs);
     std::unique_ptr<Workspace> ws0_;
+    SidePipe side_;
 };
 
 }  // namespace lsb

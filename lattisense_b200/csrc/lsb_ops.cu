@@ -633,6 +633,18 @@ void op_sum_terms(OpEnv& e, int level, int npoly, const u64* const* ct_tab, cons
 // ---------------------------------------------------------------------------------------------
 // fused chains
 // ---------------------------------------------------------------------------------------------
+// Two-stream batch pipeline (LSB_DUAL_STREAM, default on for CKKS batches of >= 256): the batch is cut in two halves
+// that run the same kernel chain on two streams, the second half one kernel behind the first, so that an FP64-pipe-bound
+// NTT launch of one half shares the SMs with an HBM-bound limb-wise launch of the other and the tail of every launch is
+// filled by the other stream's CTAs.  Same kernels on the same data: limbs are unchanged.
+static int dual_stream_min_batch() {
+    static const int v = [] {
+        const char* e = getenv("LSB_DUAL_STREAM");
+        if (e && atoi(e) == 0) return 1 << 30;
+        return e && atoi(e) > 1 ? atoi(e) : 256;
+    }();
+    return v;
+}
 static void mult_relin_chain(OpEnv& e, int level, BatchPtr a, BatchPtr b, const u64* rlk, int key_level, BatchPtr out2,
                              int batch, bool rescale) {
     LSB_CUDA(cudaSetDevice(e.c.device));
@@ -644,18 +656,35 @@ static void mult_relin_chain(OpEnv& e, int level, BatchPtr a, BatchPtr b, const 
     // [ct3 | ct2 (only when rescaling) | max(mult, relin, rescale) scratch]
     const int head = 3 * l + (rescale ? 2 * l : 0);
     const size_t item = (size_t)(head + std::max(mult_limbs, rest)) * N;
-    const int chunk = pick_chunk(e, item, batch, c.beta(level) * (l + c.np) - l);
-    u64* scratch = e.ws.reserve(item * chunk, e.s);
-    for (int b0 = 0; b0 < batch; b0 += chunk) {
-        const int nb = std::min(chunk, batch - b0);
+    auto run_chunk = [&](OpEnv& env, u64* scratch, int b0, int nb, cudaEvent_t after_first) {
         BatchPtr ct3 = bp_strided(scratch, item);
         BatchPtr ct2 = rescale ? bp_strided(scratch + (size_t)3 * l * N, item) : adv(out2, b0);
         u64* sub = scratch + (size_t)head * N;
-        if (c.scheme == SCHEME_CKKS) ckks_tensor(e, level, adv(a, b0), adv(b, b0), ct3, nb);
-        else bfv_mult_impl(e, level, adv(a, b0), adv(b, b0), ct3, sub, item, nb);
-        relin_impl(e, level, ct3, rlk, key_level, ct2, sub, item, nb);
-        if (rescale) rescale_impl(e, level, 2, ct2, adv(out2, b0), sub, item, nb);
+        if (c.scheme == SCHEME_CKKS) ckks_tensor(env, level, adv(a, b0), adv(b, b0), ct3, nb);
+        else bfv_mult_impl(env, level, adv(a, b0), adv(b, b0), ct3, sub, item, nb);
+        if (after_first) LSB_CUDA(cudaEventRecord(after_first, env.s));
+        relin_impl(env, level, ct3, rlk, key_level, ct2, sub, item, nb);
+        if (rescale) rescale_impl(env, level, 2, ct2, adv(out2, b0), sub, item, nb);
+    };
+    const bool profiling = c.dt.prof && c.dt.prof->enabled.load(std::memory_order_relaxed);
+    if (c.scheme == SCHEME_CKKS && e.chunk <= 0 && batch >= dual_stream_min_batch() && !profiling &&
+        item * (size_t)batch <= scratch_budget_words()) {
+        const int h0 = (batch + 1) / 2, h1 = batch - h0;
+        u64* scratch = e.ws.reserve(item * batch, e.s);
+        Context::SidePipe& sp = c.side_pipe();
+        OpEnv side{e.c, e.ws, sp.stream, e.chunk};
+        // the side stream may only start once everything queued on the caller's stream (its inputs) is done, and then
+        // one kernel behind the first half
+        run_chunk(e, scratch, 0, h0, sp.fork);
+        LSB_CUDA(cudaStreamWaitEvent(sp.stream, sp.fork, 0));
+        run_chunk(side, scratch + item * h0, h0, h1, nullptr);
+        LSB_CUDA(cudaEventRecord(sp.join, sp.stream));
+        LSB_CUDA(cudaStreamWaitEvent(e.s, sp.join, 0));
+        return;
     }
+    const int chunk = pick_chunk(e, item, batch, c.beta(level) * (l + c.np) - l);
+    u64* scratch = e.ws.reserve(item * chunk, e.s);
+    for (int b0 = 0; b0 < batch; b0 += chunk) run_chunk(e, scratch, b0, std::min(chunk, batch - b0), nullptr);
 }
 void op_mult_relin(OpEnv& e, int level, BatchPtr a, BatchPtr b, const u64* rlk, int key_level, BatchPtr out2,
                    int batch) {

@@ -109,6 +109,23 @@ int lsb_mult_relin(lsb_context_t ctx, int level, const uint64_t* d_a, const uint
 int lsb_mult_relin_rescale(lsb_context_t ctx, int level, const uint64_t* d_a, const uint64_t* d_b,
                            const uint64_t* d_rlk, int key_level, uint64_t* d_out2, int batch, void* stream);
 
+/* ---- CKKS bootstrapping (the `bootstrap` node: mega_ag_executors_gpu.cu:410-426, parameters gpu_wrapper.cu:106-116 /
+ * frontend/custom_task.py:424-463; algorithm: lattisense_b200/csrc/lsb_bootstrap.h) ----
+ * iparams[11] = {log_n, log_slots, cts_start_level, cts_depth, eval_mod_start_level, eval_mod_k, sine_deg, double_angle,
+ *                stc_start_level, stc_depth, output_level};  dparams[4] = {scale, cts_bsgs_ratio, message_ratio, stc_bsgs_ratio}.
+ * The plaintext matrices are encoded on the first run and stay on the device with the handle. */
+typedef struct lsb_bootstrap_st* lsb_bootstrap_t;
+lsb_bootstrap_t lsb_bootstrap_create(lsb_context_t ctx, const int* iparams, const double* dparams);
+void lsb_bootstrap_destroy(lsb_bootstrap_t h);
+/* rotation steps (mod N/2) whose Galois keys a run needs (besides the row key 2N-1); returns the count */
+int lsb_bootstrap_rotations(lsb_bootstrap_t h, int* steps, int capacity);
+/* d_ct0: [batch][2][1][N] level-0 ciphertexts; keys as the node receives them (custom_task.py:1961-1996): rlk, n_glk Galois
+ * keys with their elements (all at key_level), swk_dts (level 0), swk_std (key_level); d_out: [batch][2][out_level+1][N].
+ * stats5 (optional): rotations, key switches (all kinds), ct x ct, rescales, ct x pt. */
+int lsb_bootstrap_run(lsb_bootstrap_t h, const uint64_t* d_ct0, const uint64_t* d_rlk, int key_level, const uint64_t* galois_elements,
+                      const uint64_t* const* d_glk, int n_glk, const uint64_t* d_swk_dts, const uint64_t* d_swk_std, uint64_t* d_out,
+                      int batch, void* stream, long long* stats5);
+
 /* Launch accounting (always on) and per-kernel-class CUDA-event timing (bench.py roofline pass).
  * kind: 0 NTT fwd, 1 NTT inv, 2 basis extension, 3 key-switch inner product, 4 other limb-wise kernels. */
 long long lsb_launch_count(lsb_context_t ctx);

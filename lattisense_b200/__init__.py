@@ -77,6 +77,11 @@ def lib():
     L.lsb_ks_shard_begin_p2p.argtypes = [vp, ci, ci, ci, vp, vp, vp]
     L.lsb_ks_shard_inner_p2p.argtypes = [vp, ci, ci, ci, vp, vp, vp, vp, vp, vp]
     L.lsb_ks_shard_end.argtypes = [vp, ci, ci, ci, vp, vp, vp, vp, ci, vp]
+    L.lsb_bootstrap_create.restype = C.c_void_p
+    L.lsb_bootstrap_create.argtypes = [vp, i32p, C.POINTER(C.c_double)]
+    L.lsb_bootstrap_destroy.argtypes = [vp]
+    L.lsb_bootstrap_rotations.argtypes = [vp, i32p, ci]
+    L.lsb_bootstrap_run.argtypes = [vp, vp, vp, ci, u64p, C.POINTER(C.c_void_p), ci, vp, vp, vp, ci, vp, C.POINTER(C.c_longlong)]
     L.lsb_launch_count.restype = C.c_longlong
     L.lsb_launch_count.argtypes = [vp]
     L.lsb_profile_enable.argtypes = [vp, ci]
@@ -351,3 +356,56 @@ class Context:
 
     def mul_plain_ringt(self, ct, pt):
         return self._plain("lsb_mul_plain_ringt", ct, pt)
+
+
+class Bootstrapper:
+    """CKKS bootstrapping on the device (the `bootstrap` node, mega_ag_executors_gpu.cu:410-426) through lsb_bootstrap_*.
+    iparams / dparams as in include/lsb200.h.  Keys are uploaded once with set_keys and stay on the device."""
+
+    def __init__(self, ctx, iparams, dparams):
+        self.ctx = ctx
+        self.ip = (C.c_int * 11)(*iparams)
+        self.dp = (C.c_double * 4)(*dparams)
+        self.out_level = int(iparams[10])
+        self.h = lib().lsb_bootstrap_create(ctx.h, self.ip, self.dp)
+        if not self.h:
+            raise LsbError(lib().lsb_last_error().decode())
+        self.keys = None
+
+    def rotations(self):
+        buf = (C.c_int * 4096)()
+        n = lib().lsb_bootstrap_rotations(self.h, buf, 4096)
+        if n < 0:
+            raise LsbError(lib().lsb_last_error().decode())
+        return list(buf[:n])
+
+    def set_keys(self, rlk, gals, glks, swk_dts, swk_std):
+        c = self.ctx
+        self.keys = {"rlk": c.upload(rlk), "glk": [c.upload(k) for k in glks], "dts": c.upload(swk_dts), "std": c.upload(swk_std),
+                     "gals": np.array(gals, dtype=np.uint64), "key_level": rlk.shape[2] - c.k - 1}
+
+    def run(self, cts):
+        """cts [B][2][1][N] uint64 -> ([B][2][out_level+1][N], stats)"""
+        c, k = self.ctx, self.keys
+        cts = np.ascontiguousarray(cts, dtype=np.uint64)
+        B = cts.shape[0]
+        d_in = c.upload(cts)
+        shape = (B, 2, self.out_level + 1, c.N)
+        d_out = DevBuf(c, int(np.prod(shape)))
+        ptrs = (C.c_void_p * len(k["glk"]))(*[g.ptr for g in k["glk"]])
+        stats = (C.c_longlong * 5)()
+        _check(lib().lsb_bootstrap_run(self.h, d_in.ptr, k["rlk"].ptr, k["key_level"], k["gals"].ctypes.data_as(u64p), ptrs,
+                                       len(k["glk"]), k["dts"].ptr, k["std"].ptr, d_out.ptr, B, c.stream, stats))
+        out = c.download(d_out, shape)
+        return out, dict(zip(["rotations", "key_switches", "mults", "rescales", "plain_mults"], list(stats)))
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().lsb_bootstrap_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

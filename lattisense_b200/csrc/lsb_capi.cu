@@ -3,6 +3,7 @@
 #include <cstring>
 #include "../../include/lsb200.h"
 #include "lsb_ops.h"
+#include "lsb_bootstrap_dev.h"
 
 using namespace lsb;
 
@@ -314,6 +315,85 @@ int lsb_ks_shard_end(lsb_context_t h, int level, int world, int rank, const uint
         op_ks_shard_end(e, sp, dense(d_accP_all, (size_t)world * 2 * sp.cp * N), dense(d_acc_own, (size_t)2 * sp.n_own * N),
                         dense(d_addend_own ? d_addend_own : d_out_own, w), d_addend_own != nullptr, dense(d_out_own, w), batch);
     });
+}
+
+
+// ---- bootstrapping ----
+struct lsb_bootstrap_st {
+    lsb_context_t ctx;
+    std::unique_ptr<DeviceBootstrap> b;
+};
+lsb_bootstrap_t lsb_bootstrap_create(lsb_context_t h, const int* ip, const double* dp) {
+    LSB_API_BEGIN
+    LSB_CHECK(h && h->c && ip && dp, "lsb: null argument");
+    Context& c = *h->c;
+    btp::Params P;
+    P.logN = ip[0];
+    P.log_slots = ip[1];
+    P.q.assign(c.moduli.begin(), c.moduli.begin() + c.nq);
+    P.p.assign(c.moduli.begin() + c.nq, c.moduli.begin() + c.nq + c.np);
+    P.scale = dp[0];
+    P.cts_start = ip[2];
+    P.cts_depth = ip[3];
+    P.cts_ratio = dp[1];
+    P.evalmod_start = ip[4];
+    P.message_ratio = dp[2];
+    P.K = ip[5];
+    P.sine_deg = ip[6];
+    P.double_angle = ip[7];
+    P.stc_start = ip[8];
+    P.stc_depth = ip[9];
+    P.stc_ratio = dp[3];
+    P.out_level = ip[10];
+    auto* o = new lsb_bootstrap_st();
+    o->ctx = h;
+    try {
+        o->b.reset(new DeviceBootstrap(c, P));
+    } catch (...) {
+        delete o;
+        throw;
+    }
+    return o;
+    LSB_API_END(nullptr)
+}
+void lsb_bootstrap_destroy(lsb_bootstrap_t h) { delete h; }
+int lsb_bootstrap_rotations(lsb_bootstrap_t h, int* steps, int capacity) {
+    LSB_API_BEGIN
+    LSB_CHECK(h && h->b, "lsb: null bootstrap handle");
+    const std::vector<int> r = h->b->rotations();
+    for (int i = 0; i < (int)r.size() && i < capacity; i++) steps[i] = r[i];
+    return (int)r.size();
+    LSB_API_END(-1)
+}
+int lsb_bootstrap_run(lsb_bootstrap_t h, const uint64_t* d_ct0, const uint64_t* d_rlk, int key_level, const uint64_t* gals,
+                      const uint64_t* const* d_glk, int n_glk, const uint64_t* d_swk_dts, const uint64_t* d_swk_std, uint64_t* d_out,
+                      int batch, void* stream, long long* stats5) {
+    LSB_API_BEGIN
+    LSB_CHECK(h && h->b && h->ctx && h->ctx->c, "lsb: null bootstrap handle");
+    Context& c = *h->ctx->c;
+    std::lock_guard<std::mutex> lk(h->ctx->mu);
+    BootstrapKeys k;
+    k.rlk = d_rlk;
+    k.key_level = key_level;
+    k.swk_dts = d_swk_dts;
+    k.swk_std = d_swk_std;
+    k.swk_dts_level = 0;
+    for (int i = 0; i < n_glk; i++) {
+        k.gal.push_back(gals[i]);
+        k.glk.push_back(d_glk[i]);
+    }
+    BootstrapStats st;
+    h->b->run(c.default_workspace(), (cudaStream_t)stream, k, bp_strided(d_ct0, (size_t)2 * c.N),
+              bp_strided(d_out, (size_t)2 * (h->b->out_level() + 1) * c.N), batch, &st);
+    if (stats5) {
+        stats5[0] = st.rotations;
+        stats5[1] = st.key_switches;
+        stats5[2] = st.mults;
+        stats5[3] = st.rescales;
+        stats5[4] = st.plain_mults;
+    }
+    return 0;
+    LSB_API_END(1)
 }
 
 }  // extern "C"

@@ -529,6 +529,49 @@ void launch_ks_inner(const DeviceTables& dt, const KsInnerArgs& a, int batch, cu
     LSB_CUDA(cudaGetLastError());
 }
 
+// ---- ciphertext (op) integer constant: every limb of every polynomial times c_i, or c_i added to every NTT slot of c0 ----
+// (bootstrapping: Chebyshev constants, 2*T^2 - 1, the ScaleUp factor; reference: the constant operations inside
+//  CkksBtpContext::bootstrap / regular_bootstrapping_v2, mega_ag_executors_gpu.cu:410-426)
+struct ScalarArgs {
+    BatchPtr a, out;
+    int N, nl, add;  // add: poly 0 gets a + c, the other polynomials are copied
+    const ModConst* mods;
+    Tw c[64];
+};
+__global__ void __launch_bounds__(kElemThreads) k_scalar(const __grid_constant__ ScalarArgs g) {
+    const int j2 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j2 >= g.N / 2) return;
+    const int r = blockIdx.y, b = blockIdx.z, i = r % g.nl;
+    const u64 q = g.mods[i].q;
+    W2 x = ld2(g.a.at(b) + (size_t)r * g.N, j2);
+    if (g.add) {
+        if (r < g.nl) {
+            x.a = addmod(x.a, g.c[i].w, q);
+            x.b = addmod(x.b, g.c[i].w, q);
+        }
+    } else {
+        x.a = mul_shoup(x.a, g.c[i], q);
+        x.b = mul_shoup(x.b, g.c[i], q);
+    }
+    st2(g.out.at(b) + (size_t)r * g.N, j2, x);
+}
+void launch_scalar(const DeviceTables& dt, BatchPtr a, BatchPtr out, int npoly, int nl, const Tw* consts, bool add, int batch,
+                   cudaStream_t s) {
+    if (batch <= 0) return;
+    LSB_CHECK(nl <= 64, "scalar: too many limbs");
+    ScalarArgs g;
+    g.a = a;
+    g.out = out;
+    g.N = dt.N;
+    g.nl = nl;
+    g.add = add ? 1 : 0;
+    g.mods = dt.mods;
+    for (int i = 0; i < nl; i++) g.c[i] = consts[i];
+    ProfScope _ps(dt.prof, PK_ELEMWISE, s, 8.0 * dt.N * npoly * nl * batch * 2);
+    k_scalar<<<elem_grid(dt.N, npoly * nl, batch), kElemThreads, 0, s>>>(g);
+    LSB_CUDA(cudaGetLastError());
+}
+
 // ---- rescale ---------------------------------------------------------------------------------------------
 struct RescaleLiftArgs {
     BatchPtr last, tmp;

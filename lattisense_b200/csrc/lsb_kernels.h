@@ -125,6 +125,10 @@ struct KsInnerArgs {
 };
 void launch_ks_inner(const DeviceTables& dt, const KsInnerArgs& a, int batch, cudaStream_t s);
 
+// ct (op) per-limb integer constant (Shoup pairs): multiply every polynomial, or add to every slot of polynomial 0
+void launch_scalar(const DeviceTables& dt, BatchPtr a, BatchPtr out, int npoly, int nl, const Tw* consts, bool add, int batch,
+                   cudaStream_t s);
+
 // CKKS rescale lift: tmp[p][i] = ((last[p] + half) mod q_i) - half mod q_i, i < level
 void launch_rescale_lift(const DeviceTables& dt, BatchPtr last, int last_poly_stride, BatchPtr tmp, int npoly, int level,
                          int batch, cudaStream_t s, bool raise = false);

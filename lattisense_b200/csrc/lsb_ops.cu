@@ -10,6 +10,7 @@
 #include <cstdlib>
 #include <algorithm>
 #include "lsb_ops.h"
+#include "lsb_host_math.h"
 
 namespace lsb {
 
@@ -485,6 +486,53 @@ void op_rotate(OpEnv& e, int level, BatchPtr ct, const u64* glk, int key_level, 
         const int nb = std::min(chunk, batch - b0);
         rotate_impl(e, level, adv(ct, b0), glk, key_level, gal, adv(out, b0), scratch, item, nb);
     }
+}
+
+// Key switch without automorphism (CKKS, NTT domain): out = (c0 + KS_0(c1), KS_1(c1)) under `swk` -- the dense <-> sparse
+// secret encapsulation around ModRaise in bootstrapping (swk_dts / swk_std, frontend/custom_task.py:1989-1996)
+void op_switch_key(OpEnv& e, int level, BatchPtr ct, const u64* swk, int key_level, BatchPtr out, int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    Context& c = e.c;
+    LSB_CHECK(c.scheme == SCHEME_CKKS, "lsb: switch_key is a CKKS (NTT-domain) operation");
+    const int l = level + 1;
+    const size_t N = c.N;
+    const size_t item = (size_t)(l + ks_scratch_limbs(c, level)) * N;
+    const int chunk = pick_chunk(e, item, batch, c.beta(level) * (l + c.np) - l);
+    u64* scratch = e.ws.reserve(item * chunk, e.s);
+    for (int b0 = 0; b0 < batch; b0 += chunk) {
+        const int nb = std::min(chunk, batch - b0);
+        BatchPtr c1x = bp_strided(scratch, item);
+        launch_ntt(c.dt, adv(ct, b0), c1x, rowmap_seq(l, l, 0, 0, l), nb, true, e.s);
+        ks_core(e, level, c1x, 0, adv(ct, b0), l, swk, key_level, adv(ct, b0), 1, adv(out, b0), l, scratch + (size_t)l * N, item, nb);
+    }
+}
+
+// first level_to+1 limbs of every polynomial (drop_level applied level_from - level_to times)
+void op_drop_to(OpEnv& e, int level_from, int level_to, int npoly, BatchPtr in, BatchPtr out, int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    LSB_CHECK(level_to >= 0 && level_to <= level_from, "lsb: drop_to: bad levels");
+    const int lf = level_from + 1, lt = level_to + 1;
+    RowMap m;
+    m.n = npoly * lt;
+    LSB_CHECK(m.n <= kMaxRows, "lsb: too many limbs");
+    for (int p = 0; p < npoly; p++)
+        for (int i = 0; i < lt; i++) {
+            const int r = p * lt + i;
+            m.in_slot[r] = (uint8_t)(p * lf + i);
+            m.out_slot[r] = (uint8_t)r;
+            m.mod[r] = (uint8_t)i;
+        }
+    launch_binary(e.c.dt, OP_ADD, in, in, out, m, 0, batch, e.s);
+}
+
+// ct times / plus an integer constant given as residues modulo q_0..q_level
+void op_scalar(OpEnv& e, int level, int npoly, BatchPtr ct, const u64* residues, bool add, BatchPtr out, int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    const int l = level + 1;
+    LSB_CHECK(l <= 64, "lsb: too many limbs");
+    Tw consts[64];
+    for (int i = 0; i < l; i++) consts[i] = host::make_tw(residues[i] % e.c.moduli[i], e.c.moduli[i]);
+    launch_scalar(e.c.dt, ct, out, npoly, l, consts, add, batch, e.s);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -26,6 +26,10 @@ void op_mod_raise(OpEnv& e, int top_level, int npoly, BatchPtr in, BatchPtr out,
 void op_linear_transform(OpEnv& e, int level, const u64* ct, int n_diag, const int* diag_rot, const u64* const* diag_pt, int n1,
                          int n_keys, const int* key_rot, const u64* const* glk, int key_level, u64* out);
 void op_drop_level(OpEnv& e, int level, int npoly, BatchPtr in, BatchPtr out, int batch);
+void op_drop_to(OpEnv& e, int level_from, int level_to, int npoly, BatchPtr in, BatchPtr out, int batch);
+// key switch without automorphism (bootstrapping's swk_dts / swk_std) and ct (op) integer constant
+void op_switch_key(OpEnv& e, int level, BatchPtr ct, const u64* swk, int key_level, BatchPtr out, int batch);
+void op_scalar(OpEnv& e, int level, int npoly, BatchPtr ct, const u64* residues, bool add, BatchPtr out, int batch);
 // bind_gpu_rotate_col / bind_gpu_rotate_row (:264-292): automorphism gal + key-switch under glk[gal]
 void op_rotate(OpEnv& e, int level, BatchPtr ct, const u64* glk, int key_level, u64 gal, BatchPtr out, int batch);
 // bind_gpu_add / sub / neg (:71-175), ct (op) ct with npoly polynomials

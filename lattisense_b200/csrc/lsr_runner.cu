@@ -31,6 +31,7 @@
 #include "lattisense_gpu_runner.h"
 #include "lattisense_mega_ag.hpp"
 #include "lsb_ops.h"
+#include "lsb_bootstrap_dev.h"
 #include "lsr_graph.h"
 
 namespace lsr {
@@ -220,6 +221,9 @@ struct DeviceRuntime {
     u64** tab_dev = nullptr;
     size_t tab_cap = 0, tab_head = 0;
     cudaEvent_t tab_wrap_ev = nullptr;
+    // bootstrapping precompute (encoded CoeffsToSlots / SlotsToCoeffs matrices), built at the first bootstrap node and
+    // kept with the task: the analogue of generate_bootstrapping_params_v2 in init_gpu_context (gpu_wrapper.cu:106-116)
+    std::unique_ptr<lsb::DeviceBootstrap> btp;
 
     ~DeviceRuntime() {
         cudaSetDevice(device);
@@ -231,6 +235,7 @@ struct DeviceRuntime {
         if (tab_host) cudaFreeHost(tab_host);
         if (tab_dev) cudaFree(tab_dev);
         if (tab_wrap_ev) cudaEventDestroy(tab_wrap_ev);
+        btp.reset();
         ws.reset();
         ctx.reset();
         if (compute) cudaStreamDestroy(compute);
@@ -994,7 +999,7 @@ void RunState::start_store_unit(const Unit& u) {
 // ---------------------------------------------------------------------------------------------
 enum CallKind {
     K_ADD_CC, K_SUB_CC, K_ADD_CP, K_ADD_CPR, K_SUB_PC, K_SUB_PRC, K_NEG, K_MULT_CC, K_MUL_CP, K_MUL_CPR, K_RELIN, K_RESCALE,
-    K_DROP, K_ROTATE, K_MAC, K_MULT_RELIN, K_MULT_RELIN_RESCALE, K_SUM
+    K_DROP, K_ROTATE, K_MAC, K_MULT_RELIN, K_MULT_RELIN_RESCALE, K_SUM, K_BOOTSTRAP
 };
 struct GpuCall {
     int kind = 0, level = 0, npoly = 2, aux = 0, aux2 = 0;  // aux: subtract flag / ringt flag / sum_cnt ; aux2: has partial sum
@@ -1003,6 +1008,7 @@ struct GpuCall {
     uint64_t gal = 0;
     std::vector<DevObjPtr> operands;  // inputs in the canonical order of the kind
     std::vector<DevObjPtr> keepalive;
+    std::shared_ptr<lsb::BootstrapKeys> btp_keys;  // K_BOOTSTRAP: rlk, Galois keys by element, swk_dts, swk_std
     int out_level = 0, out_npoly = 2;
     std::string signature(int slot) const {
         char buf[160];
@@ -1011,6 +1017,43 @@ struct GpuCall {
         return buf;
     }
 };
+
+// bootstrapping parameters as the frontend writes them into mega_ag.json (custom_task.py CkksBtpParam.to_dict; the same
+// fields init_gpu_context reads, gpu_wrapper.cu:92-116)
+static lsb::btp::Params btp_params(const TaskGraph& g) {
+    const Json& j = g.parameter;
+    auto geti = [&](const char* k) {
+        LSB_CHECK(j.contains(k), std::string("mega_ag: parameter '") + k + "' is missing");
+        return j.at(k).as_int();
+    };
+    auto getd = [&](const char* k, double dflt) { return j.contains(k) ? j.at(k).as_double() : dflt; };
+    lsb::btp::Params P;
+    P.logN = 0;
+    while ((1 << P.logN) < g.param.n) P.logN++;
+    const int slots = j.contains("slots") ? j.at("slots").as_int() : g.param.n / 2;
+    P.log_slots = 0;
+    while ((1 << P.log_slots) < slots) P.log_slots++;
+    P.q.assign(g.param.q.begin(), g.param.q.begin() + g.param.max_level + 1);
+    P.p = g.param.p;
+    P.scale = getd("scale", 0.0);
+    P.cts_start = geti("btp_cts_start_level");
+    P.cts_depth = geti("btp_cts_depth");
+    P.cts_ratio = getd("btp_cts_bsgs_ratio", 2.0);
+    P.evalmod_start = geti("btp_eval_mod_start_level");
+    P.message_ratio = getd("btp_eval_mod_message_ratio", 256.0);
+    P.K = geti("btp_eval_mod_k");
+    P.sine_deg = geti("btp_eval_mod_sine_deg");
+    P.double_angle = geti("btp_eval_mod_double_angle");
+    LSB_CHECK(!j.contains("btp_eval_mod_arcsine_deg") || j.at("btp_eval_mod_arcsine_deg").as_int() == 0,
+              "lsb runner: bootstrapping with an arcsine correction is not supported");
+    LSB_CHECK(!j.contains("btp_eval_mod_sine_type") || j.at("btp_eval_mod_sine_type").as_string() == "Cos1",
+              "lsb runner: only the Cos1 EvalMod variant is supported");
+    P.stc_start = geti("btp_stc_start_level");
+    P.stc_depth = geti("btp_stc_depth");
+    P.stc_ratio = getd("btp_stc_bsgs_ratio", 2.0);
+    P.out_level = geti("btp_output_level");
+    return P;
+}
 
 namespace {
 enum PtKind { PT_NONE, PT_PLAIN, PT_RINGT };
@@ -1073,8 +1116,16 @@ GpuCall RunState::describe(const Unit& u, const std::unordered_map<NodeIndex, st
     switch (op) {
         case OperationType::ADD:
         case OperationType::SUB: {
-            need(2);
+            need(1);
             const bool sub = op == OperationType::SUB;
+            if (ins.size() == 1) {  // x (op) x: the frontend emits ONE edge (mega_ag_executors_gpu.cu:72-80, 124-132)
+                LSB_CHECK(pt_kind(ins[0]) == PT_NONE, "lsb runner: add/sub of a single plaintext is not a ciphertext operation");
+                c.kind = sub ? K_SUB_CC : K_ADD_CC;
+                c.level = ins[0]->fhe_prop->level;
+                c.npoly = ins[0]->fhe_prop->degree + 1;
+                c.operands = {dev(ins[0]), dev(ins[0])};
+                break;
+            }
             const PtKind p0 = pt_kind(ins[0]), p1 = pt_kind(ins[1]);
             if (p0 == PT_NONE && p1 == PT_NONE) {
                 c.kind = sub ? K_SUB_CC : K_ADD_CC;
@@ -1186,8 +1237,51 @@ GpuCall RunState::describe(const Unit& u, const std::unordered_map<NodeIndex, st
             for (int i = 0; i < (int)ins.size(); i++) c.operands.push_back(dev(ins[i]));
             break;
         }
-        case OperationType::BOOTSTRAP:
-            throw std::runtime_error("lsb runner: CKKS bootstrapping is not implemented on this backend yet (node '" + n0.id + "')");
+        case OperationType::BOOTSTRAP: {
+            // inputs [ct, rlk, glk..., swk_dts, swk_std] (mega_ag_executors_gpu.cu:415-419, custom_task.py:1961-1996)
+            need(5);
+            LSB_CHECK(g.algo == ALGO_CKKS && g.param.has_btp, "lsb runner: bootstrap needs a CKKS task with btp_* parameters (node '" + n0.id + "')");
+            LSB_CHECK(ins[0]->fhe_prop->level == 0 && ins[0]->fhe_prop->degree == 1, "lsb runner: bootstrap input must be a level-0 ciphertext");
+            c.kind = K_BOOTSTRAP;
+            c.level = 0;
+            c.operands = {dev(ins[0])};
+            auto keys = std::make_shared<lsb::BootstrapKeys>();
+            int n_swk = 0;
+            for (size_t i = 1; i < ins.size(); i++) {
+                DevObjPtr k = dev(ins[i]);
+                c.keepalive.push_back(k);
+                switch (ins[i]->datum_type) {
+                    case TYPE_RELIN_KEY:
+                        keys->rlk = k->ptr;
+                        keys->key_level = k->level;
+                        break;
+                    case TYPE_GALOIS_KEY:
+                        LSB_CHECK(ins[i]->fhe_prop->p.has_value() && ins[i]->fhe_prop->p->galois_element, "mega_ag: Galois key '" + ins[i]->id + "' carries no element");
+                        keys->gal.push_back(ins[i]->fhe_prop->p->galois_element);
+                        keys->glk.push_back(k->ptr);
+                        LSB_CHECK(k->level == g.param.max_level, "lsb runner: bootstrap Galois keys must be at the top level");
+                        break;
+                    case TYPE_SWITCH_KEY:
+                        // the last two inputs: swk_dts (level 0) then swk_std (top level)
+                        if (n_swk == 0) {
+                            keys->swk_dts = k->ptr;
+                            keys->swk_dts_level = k->level;
+                        } else {
+                            keys->swk_std = k->ptr;
+                            LSB_CHECK(k->level == g.param.max_level, "lsb runner: swk_std must be at the top level");
+                        }
+                        n_swk++;
+                        break;
+                    default: throw std::runtime_error("mega_ag: unexpected input '" + ins[i]->id + "' of bootstrap node '" + n0.id + "'");
+                }
+            }
+            LSB_CHECK(keys->rlk && keys->swk_dts && keys->swk_std && n_swk == 2 && !keys->glk.empty(), "mega_ag: bootstrap node '" + n0.id + "' lacks a key input");
+            LSB_CHECK(keys->key_level == g.param.max_level, "lsb runner: the bootstrap relinearisation key must be at the top level");
+            c.key = keys->rlk;
+            c.key_level = keys->key_level;
+            c.btp_keys = keys;
+            break;
+        }
         default: throw std::runtime_error("lsb runner: unsupported operation in node '" + n0.id + "'");
     }
     return c;
@@ -1294,6 +1388,13 @@ void RunState::exec_group(int slot, const std::vector<int>& members, const GpuCa
         case K_ROTATE: lsb::op_rotate(e, L, tabs[0], rep.key, rep.key_level, rep.gal, out, nb); break;
         case K_MULT_RELIN: lsb::op_mult_relin(e, L, tabs[0], tabs[1], rep.key, rep.key_level, out, nb); break;
         case K_MULT_RELIN_RESCALE: lsb::op_mult_relin_rescale(e, L, tabs[0], tabs[1], rep.key, rep.key_level, out, nb); break;
+        case K_BOOTSTRAP: {
+            if (!rt->btp) rt->btp.reset(new lsb::DeviceBootstrap(ctx, btp_params(g)));
+            LSB_CHECK(rt->btp->out_level() == rep.out_level, "lsb runner: bootstrap output level differs from btp_output_level");
+            lsb::BootstrapStats st;
+            rt->btp->run(*rt->ws, rt->compute, *rep.btp_keys, tabs[0], out, nb, &st);
+            break;
+        }
         case K_MAC: {
             const int cnt = rep.npoly, acc = rep.aux2;
             lsb::op_mac(e, L, cnt, tabs.data(), tabs.data() + cnt + acc, rep.aux != 0, acc != 0, acc ? tabs[cnt] : out, out, nb);

@@ -280,8 +280,154 @@ def gen_cfg3_replicas(copies=8):
     emit(f"cfg3_bfv_poly7_x{copies}", [Argument("x", xs), Argument("a", a), Argument("a_0", a0)], [Argument("y", ys)])
 
 
+def gen_bootstrap():
+    """The reference's bootstrap GPU cases (unittests/test_gpu_ckks.py:566-614 / test_gpu_ckks.cpp:743-808): toy_bootstrap
+    (n = 8192), bootstrap and cmc_relin_rescale_bootstrap (n = 65536), on the N16QP1546H192H32 chain."""
+    set_fhe_param(CkksBtpParam.create_toy_param())
+    xs = [CkksCiphertextNode(f"x_{i}", level=0) for i in range(2)]
+    ys = [bootstrap(xs[i], f"y_{i}") for i in range(2)]
+    emit("ckks_btp8k_toy_bootstrap", [Argument("in_x_list", xs)], [Argument("out_y_list", ys)])
+
+    set_fhe_param(CkksBtpParam.create_default_param())
+    xs = [CkksCiphertextNode("x_0", level=0)]
+    ys = [bootstrap(xs[0], "y_0")]
+    emit("ckks_btp64k_bootstrap", [Argument("in_x_list", xs)], [Argument("out_y_list", ys)])
+
+    p = CkksBtpParam.create_toy_param()
+    set_fhe_param(p)
+    lv = 3
+    xs = [CkksCiphertextNode("x_0", level=lv)]
+    ys = [CkksCiphertextNode("y_0", level=lv)]
+    z = rescale(mult_relin(xs[0], ys[0]))
+    zd = drop_level(z, z.level)
+    res = [bootstrap(zd, "result_0")]
+    emit("ckks_btp8k_cmc_relin_rescale_bootstrap", [Argument("in_x_list", xs), Argument("in_y_list", ys)],
+         [Argument("out_z_list", res)])
+
+
+def gen_reference_extras():
+    """Reference GPU cases that had no fixture: unittests/test_gpu_bfv.py:116-549, test_gpu_ckks.py:233."""
+    for tag, mkparam, Ct, lv in (("bfv8k", bfv8k, BfvCiphertextNode, 2), ("ckks8k", ckks8k, CkksCiphertextNode, 4)):
+        set_fhe_param(mkparam())
+        xs = [Ct(f"x_{i}", level=lv) for i in range(N_OP)]
+        emit(f"{tag}_casc", [Argument("in_x_list", xs)], [Argument("out_z_list", [add(xs[i], xs[i], f"z_{i}") for i in range(N_OP)])])
+        set_fhe_param(mkparam())
+        xs = [Ct(f"x_{i}", level=lv) for i in range(N_OP)]
+        emit(f"{tag}_cssc", [Argument("in_x_list", xs)], [Argument("out_z_list", [sub(xs[i], xs[i], f"z_{i}") for i in range(N_OP)])])
+        set_fhe_param(mkparam())
+        xs = [Ct(f"x_{i}", level=lv) for i in range(N_OP)]
+        emit(f"{tag}_csqr", [Argument("in_x_list", xs)], [Argument("out_z_list", [mult(xs[i], xs[i], f"z_{i}") for i in range(N_OP)])])
+        set_fhe_param(mkparam())
+        xs = [Ct(f"x_{i}", level=lv) for i in range(N_OP)]
+        emit(f"{tag}_csqr_relin", [Argument("in_x_list", xs)],
+             [Argument("out_z_list", [mult_relin(xs[i], xs[i], f"z_{i}") for i in range(N_OP)])])
+
+    bfv16 = lambda: BfvParam.create_default_param(n=16384)
+    Ct, lv = BfvCiphertextNode, 3
+    set_fhe_param(bfv16())
+    xs = [Ct(f"x_{i}", level=lv) for i in range(4)]
+    ys = [Ct(f"y_{i}", level=lv) for i in range(4)]
+    tmp0 = mult_relin(xs[0], ys[0], "tmp_0")
+    zs = [tmp0, mult_relin(tmp0, xs[1], "z_0"), mult_relin(xs[1], ys[1], "z_1"), mult_relin(xs[2], ys[2], "z_2"),
+          mult_relin(xs[3], ys[3], "z_3")]
+    emit("bfv16k_ctc_ctc_0", [Argument("in_x_list", xs), Argument("in_y_list", ys)], [Argument("out_z_list", zs)])
+
+    set_fhe_param(bfv16())
+    xs = [Ct(f"x_{i}", level=lv) for i in range(4)]
+    ys = [Ct(f"y_{i}", level=lv) for i in range(4)]
+    t = [mult_relin(xs[i], ys[i], f"t_{i}") for i in range(4)]
+    zs = [mult_relin(t[0], t[1], "z_0"), mult_relin(t[1], xs[2], "z_1"), mult_relin(t[2], xs[3], "z_2"), mult_relin(t[2], t[3], "z_3")]
+    emit("bfv16k_ctc_ctc_1", [Argument("in_x_list", xs), Argument("in_y_list", ys)], [Argument("out_z_list", zs)])
+
+    set_fhe_param(bfv16())
+    xs = [Ct("x_0", level=lv)]
+    t = mult_relin(xs[0], xs[0], "x^2_0")
+    emit("bfv16k_1_square_square", [Argument("in_x_list", xs)], [Argument("out_z_list", [mult_relin(t, t, "x^4_0")])])
+
+    set_fhe_param(bfv16())
+    xs = [Ct(f"x_{i}", level=lv) for i in range(3)]
+    emit("bfv16k_double", [Argument("in_x_list", xs)],
+         [Argument("out_z_list", [mult_relin(xs[0], xs[1], "z_0"), mult_relin(xs[0], xs[2], "z_1")])])
+
+    set_fhe_param(bfv16())
+    ins = [Ct(f"x_{i}", level=lv) for i in range(4)]
+    x = ins
+    for i in range(2):
+        x = [mult_relin(x[j], x[(j + 1) % 4], f"y_{i * 4 + j}") for j in range(4)]
+    emit("bfv16k_braid", [Argument("in_list", ins)], [Argument("out_list", x)])
+
+    set_fhe_param(bfv16())
+    xs = [Ct(f"x_{i}", level=lv) for i in range(4)]
+    co = [Ct(f"coeffs_{i}", level=lv) for i in range(3)]
+    zs = []
+    for i in range(4):
+        ax = mult_relin(xs[i], co[0], f"ax_{i}")
+        ax2 = mult_relin(ax, xs[i], f"ax2_{i}")
+        bx = mult_relin(co[1], xs[i], f"bx_{i}")
+        zs.append(add(add(ax2, bx, f"ax2_bx_{i}"), co[2], f"ax2_bx_c_{i}"))
+    emit("bfv16k_poly", [Argument("in_x_list", xs), Argument("in_a_list", co)], [Argument("out_z_list", zs)])
+
+    # CKKS ct x pt multiply-accumulate with NTT-domain plaintexts (test_gpu_ckks.py:233: m = 2..20)
+    for m in (2, 5, 20):
+        set_fhe_param(CkksParam.create_default_param(n=16384))
+        cs = [CkksCiphertextNode(f"c_{i}", level=2) for i in range(m)]
+        ps = [CkksPlaintextNode(f"p_{i}", level=2) for i in range(m)]
+        z = ct_pt_mult_accumulate(cs, ps)
+        emit(f"ckks16k_ct_pt_mac_m{m}", [Argument("in_c_list", cs), Argument("in_p_list", ps)], [Argument("out_z_list", [z])])
+
+    # default-parameter (n = 16384) level sweeps of the two hot-path cases
+    for lv in (1, 3, 5):
+        set_fhe_param(CkksParam.create_default_param(n=16384))
+        xs = [CkksCiphertextNode(f"x_{i}", level=lv) for i in range(2)]
+        ys = [CkksCiphertextNode(f"y_{i}", level=lv) for i in range(2)]
+        zs = [rescale(mult_relin(xs[i], ys[i]), f"z_{i}") for i in range(2)]
+        emit(f"ckks16k_cmc_relin_rescale_l{lv}", [Argument("in_x_list", xs), Argument("in_y_list", ys)], [Argument("out_z_list", zs)])
+        set_fhe_param(CkksParam.create_default_param(n=16384))
+        xs = [CkksCiphertextNode(f"x_{i}", level=lv) for i in range(2)]
+        ys = [rotate_cols(xs[i], [1, 3]) for i in range(2)]
+        emit(f"ckks16k_rotate_col_l{lv}", [Argument("in_x_list", xs)], [Argument("out_y_list", ys)])
+    for lv in (1, 3, 5):
+        set_fhe_param(BfvParam.create_default_param(n=16384))
+        xs = [BfvCiphertextNode(f"x_{i}", level=lv) for i in range(2)]
+        ys = [BfvCiphertextNode(f"y_{i}", level=lv) for i in range(2)]
+        zs = [rescale(mult_relin(xs[i], ys[i]), f"z_{i}") for i in range(2)]
+        emit(f"bfv16k_cmc_relin_rescale_l{lv}", [Argument("in_x_list", xs), Argument("in_y_list", ys)], [Argument("out_z_list", zs)])
+        set_fhe_param(BfvParam.create_default_param(n=16384))
+        xs = [BfvCiphertextNode(f"x_{i}", level=lv) for i in range(2)]
+        ys = [rotate_cols(xs[i], [1, 3]) for i in range(2)]
+        emit(f"bfv16k_rotate_col_l{lv}", [Argument("in_x_list", xs)], [Argument("out_y_list", ys)])
+
+    # sparse-slot CKKS parameter set (test_gpu_ckks.py:47-48): slots only matter to encode/decode
+    set_fhe_param(ckks8k())
+    p = CkksParam.create_custom_param(n=CKKS8K["n"], q=list(CKKS8K["q"]), p=list(CKKS8K["p"]), scale=CKKS8K["scale"])
+    p.set_slots(2048)
+    set_fhe_param(p)
+    xs = [CkksCiphertextNode(f"x_{i}", level=4) for i in range(2)]
+    ys = [CkksCiphertextNode(f"y_{i}", level=4) for i in range(2)]
+    zs = [rescale(mult_relin(xs[i], ys[i]), f"z_{i}") for i in range(2)]
+    emit("ckks8k_sparse_cmc_relin_rescale", [Argument("in_x_list", xs), Argument("in_y_list", ys)], [Argument("out_z_list", zs)])
+
+    # custom node at the end of the graph (test_gpu_bfv.py:650-676), mapped onto the harness' "passthrough" executor
+    set_fhe_param(bfv8k())
+    xs = [BfvCiphertextNode(f"x_{i}", level=2) for i in range(N_OP)]
+    ys = [BfvCiphertextNode(f"y_{i}", level=2) for i in range(N_OP)]
+    ms = [relin(mult(xs[i], ys[i], f"x_mult_y_{i}"), f"m_{i}") for i in range(N_OP)]
+    zs = []
+    for i in range(N_OP):
+        zi = BfvCiphertextNode(f"z_{i}", level=2)
+        custom_compute(inputs=[ms[i]], output=zi, type="passthrough")
+        zs.append(zi)
+    emit("bfv8k_custom_at_end", [Argument("in_x_list", xs), Argument("in_y_list", ys)], [Argument("out_z_list", zs)])
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if sys.argv[1:] == ["btp"]:
+        gen_bootstrap()
+        sys.exit(0)
+    if sys.argv[1:] == ["extras"]:
+        gen_reference_extras()
+        sys.exit(0)
     if sys.argv[1:] == ["cfg3x"]:
         gen_cfg3_replicas(8)
         gen_cfg3_replicas(64)  # throughput fixture for tools/multi_device_run.py; gzip it after generation

@@ -99,6 +99,19 @@ class GraphCase:
         self.compute = {int(k): v for k, v in self.g["compute"].items()}
         self.values = {}
         self.secret = self.o.gen_secret(seed)
+        self.btp = None
+        if any(c["type"] == "bootstrap" for c in self.compute.values()):
+            # bootstrap graphs need real key material and real encryptions: dense secret of weight 192, ephemeral
+            # sparse secret of weight 32 behind swk_dts / swk_std (what CkksBtpContext generates on the reference side)
+            import btp_ref as B
+            p = self.g["parameter"]
+            self.btp = B.BtpSpec(self.params, p["btp_cts_start_level"], p["btp_cts_depth"], p["btp_eval_mod_start_level"],
+                                 p["btp_eval_mod_k"], p["btp_eval_mod_sine_deg"], p["btp_eval_mod_double_angle"],
+                                 p["btp_stc_start_level"], p["btp_stc_depth"], p["btp_output_level"],
+                                 p["btp_eval_mod_message_ratio"], p["btp_cts_bsgs_ratio"])
+            self.secret = B.fixed_weight_secret(self.N, 192, seed)
+            self.secret_sparse = B.fixed_weight_secret(self.N, 32, seed + 1)
+            self.messages = {}
         self._make_inputs(seed)
 
     # ---- inputs ----
@@ -115,7 +128,11 @@ class GraphCase:
         for idx in self.g["inputs"]:
             d = self.data[idx]
             t, lv = d["type"], d["level"]
-            if t in ("ct", "ct3"):
+            if t in ("ct", "ct3") and self.btp is not None:
+                z = self.rng.uniform(-1, 1, self.N // 2) + 1j * self.rng.uniform(-1, 1, self.N // 2)
+                self.messages[idx] = z
+                self.values[idx] = self.o.encrypt(self.secret, seed + 100 + idx, lv, R.ckks_encode(self.o, z, lv, self.params.scale))
+            elif t in ("ct", "ct3"):
                 self.values[idx] = self._rand_limbs((d["degree"] + 1,), q[:lv + 1])
             elif t in ("pt", "pt_mul"):
                 if self.pt_pool:
@@ -128,6 +145,12 @@ class GraphCase:
             elif t == "pt_ringt":
                 tt = self.params.t if self.params.scheme == R.SCHEME_BFV else 65537
                 self.values[idx] = self.rng.integers(0, tt, size=(1, self.N), dtype=np.uint64)
+            elif t == "swk" and self.btp is not None:
+                import btp_ref as B
+                evk = np.zeros(self.o.evk_shape(lv), dtype=np.uint64)
+                s_in, s_out = (self.secret, self.secret_sparse) if d["id"] == "swk_dts" else (self.secret_sparse, self.secret)
+                B.lib().orc_gen_swk(self.o.hp, s_in.ctypes.data_as(B.i8p), s_out.ctypes.data_as(B.i8p), C.c_uint64(seed + 4 + lv), lv, R.P(evk))
+                self.values[idx] = evk
             elif t in ("rlk", "swk"):
                 # a real key for the task's secret at the node's level (uniform limbs would do for parity, but
                 # real keys let the decode-level checks run on the same data)
@@ -163,7 +186,7 @@ class GraphCase:
         bfv = self.params.scheme == R.SCHEME_BFV
         kind = lambda i: D[i]["type"]
         if t in ("add", "sub"):
-            a, b = ins
+            a, b = ins if len(ins) == 2 else (ins[0], ins[0])
             fn = o.add if t == "add" else o.sub
             if kind(a) in ("ct", "ct3") and kind(b) in ("ct", "ct3"):
                 return fn(V[a], V[b])
@@ -212,6 +235,21 @@ class GraphCase:
                 acc = term if acc is None else o.add(acc, term)
             out = self._to_native(acc)
             return o.add(out, acc_in) if acc_in is not None else out
+        if t == "bootstrap":
+            import btp_ref as B
+
+            class K:
+                pass
+            k = K()
+            k.rlk = V[ins[1]]
+            k.top = D[ins[1]]["level"]
+            glk_ids = [i for i in ins[2:] if kind(i) == "glk"]
+            k.gals = [int(D[i]["galois_element"]) for i in glk_ids]
+            k.glk = [V[i] for i in glk_ids]
+            swk = [i for i in ins if kind(i) == "swk"]
+            k.swk_dts, k.swk_std = V[swk[0]], V[swk[1]]
+            out, self.btp_stats = B.oracle_bootstrap(o, self.btp, k, V[ins[0]][None])
+            return out[0]
         if c.get("is_custom"):
             if t == "passthrough":
                 return V[ins[0]]

@@ -143,6 +143,13 @@ struct ComputeNode {
     std::optional<CustomProperty> custom_prop;
 };
 
+// mega_ag_executors.h:53-54 (implementation mega_ag_executors_gpu.cu:463-512).  A caller that still links the reference's
+// mega_ag.cpp (liblattisense.so, CMakeLists.txt:360-364) resolves this symbol while loading a graph.  This backend does
+// not execute device nodes one by one -- run_fhe_gpu_task groups them into batched launches -- so the binder validates
+// the (algorithm, operation) pair exactly as the reference does (same exceptions for unsupported pairs) and installs an
+// executor that reports, if anybody calls it, that the node belongs to the batched dispatcher.
+void bind_gpu_executor(ComputeNode& node, Algo algorithm);
+
 // Optional hook (extension): EXPORT/IMPORT/custom executors of the in-tree SDK require an "empty frontend
 // context" (BfvContext* / CkksContext* / CkksBtpContext*, gpu_wrapper.cu:175-177) in ExecutionContext::context.
 // A caller that links liblattigo installs a factory producing that std::any from the task's `parameter`

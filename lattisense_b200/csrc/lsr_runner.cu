@@ -299,7 +299,9 @@ struct DeviceObject {
         if (!rt) return;
         cudaSetDevice(rt->device);
         // all consumers were enqueued on the compute stream (or finished, for stores) before the last
-        // reference is dropped, so a free ordered on that stream is safe
+        // reference is dropped, so a free ordered on that stream is safe -- once that stream also waits for the copy
+        // that PRODUCED the object (a LOADed object of a failed / cancelled run may never have had a consumer)
+        if (ptr && ready) cudaStreamWaitEvent(rt->compute, ready, 0);
         if (ptr) cudaFreeAsync(ptr, rt->compute);
         if (ready) cudaEventDestroy(ready);
     }
@@ -600,15 +602,18 @@ static std::vector<int> assign_components(const Plan& p, int n_slots) {
 struct GpuTask {
     std::unique_ptr<TaskGraph> graph;
     Plan plan;
-    std::map<int, std::unique_ptr<DeviceRuntime>> runtimes;  // by CUDA device index, built on first use
+    // by (CUDA device index, ordinal of the slot on that device), built on first use: lsb_gpu_task_set_devices may name a
+    // device twice -- two independent slots (streams, dispatcher, staging rings, tables) sharing one GPU
+    std::map<std::pair<int, int>, std::unique_ptr<DeviceRuntime>> runtimes;
     std::vector<int> devices;                                // lsb_gpu_task_set_devices; empty: run()'s gpu_device
     FrontendContextFactory ctx_factory;
     std::mutex run_mu;  // one run at a time per handle (like the reference: FheTask::input_args is reused)
     long long stat_launches = 0, stat_groups = 0, stat_fused = 0;
 
-    DeviceRuntime* runtime(int device) {
-        auto it = runtimes.find(device);
-        if (it == runtimes.end()) it = runtimes.emplace(device, make_device_runtime(device, *graph)).first;
+    DeviceRuntime* runtime(int device, int ordinal = 0) {
+        const std::pair<int, int> key(device, ordinal);
+        auto it = runtimes.find(key);
+        if (it == runtimes.end()) it = runtimes.emplace(key, make_device_runtime(device, *graph)).first;
         return it->second.get();
     }
 };
@@ -1233,6 +1238,14 @@ GpuCall RunState::describe(const Unit& u, const std::unordered_map<NodeIndex, st
             c.aux2 = with_acc ? 1 : 0;
             const DatumNode* pt0 = ins[cnt + (with_acc ? 1 : 0)];
             c.aux = pt_kind(pt0) == PT_RINGT ? 1 : 0;
+            for (int i = 0; i < cnt; i++) {
+                const DatumNode* pti = ins[cnt + (with_acc ? 1 : 0) + i];
+                LSB_CHECK(pt_kind(pti) == pt_kind(pt0) && pt_kind(pti) != PT_NONE, "mega_ag: MAC node '" + n0.id + "' mixes plaintext kinds");
+                // reference: 'Multiply with plaintext only supported for CKKS' (mega_ag_executors_gpu.cu:202-213); here a BFV
+                // plaintext is accepted when it is a pt_mul (NTT domain), never a coefficient-domain scaled plaintext
+                if (g.algo == ALGO_BFV && pt_kind(pti) == PT_PLAIN)
+                    LSB_CHECK(pti->fhe_prop->is_ntt, "lsb runner: BFV multiply-accumulate needs pt_ringt or pt_mul operands (node '" + n0.id + "')");
+            }
             c.npoly = cnt;  // number of terms
             for (int i = 0; i < (int)ins.size(); i++) c.operands.push_back(dev(ins[i]));
             break;
@@ -1565,9 +1578,12 @@ static int run_task(GpuTask& task, CArgument* input_args, uint64_t n_in, CArgume
     static WorkerPool pool(nthreads);  // shared by all tasks of the process
     RunState rs(task, pool, cb, ud);
     long long launches0 = 0;
-    for (int d : devs) {
-        rs.slots.push_back(task.runtime(d));
-        launches0 += rs.slots.back()->ctx->prof.launches.load();
+    {
+        std::map<int, int> seen;
+        for (int d : devs) {
+            rs.slots.push_back(task.runtime(d, seen[d]++));
+            launches0 += rs.slots.back()->ctx->prof.launches.load();
+        }
     }
     rs.slot_of_component = assign_components(task.plan, (int)devs.size());
     if (task.ctx_factory) rs.frontend_ctx = task.ctx_factory(g.algo, json_dump(g.parameter));
@@ -1635,6 +1651,12 @@ static int run_task(GpuTask& task, CArgument* input_args, uint64_t n_in, CArgume
         for (int q = 1; q < (int)devs.size(); q++) others.emplace_back(serve, q);
         serve(0);
         for (auto& t : others) t.join();
+    }
+    {
+        // tasks already handed to the process-wide worker pool capture `rs`: on an aborted run the dispatchers return
+        // early, so wait here until every one of them has finished (they return quickly once `failed` is set)
+        std::unique_lock<std::mutex> lk(rs.mu);
+        rs.cv.wait(lk, [&] { return rs.in_flight == 0; });
     }
 
     for (DeviceRuntime* rt : rs.slots) {

@@ -4,6 +4,8 @@
   lsb_bootstrap.h with the CPU oracle's ciphertext operations) on the reference's 25 + 5 prime chain at toy ring degrees;
 * precision: decrypt + decode of the device result against the encrypted message, >= 10 bits mean real precision (the
   reference's bound) at the toy degree n = 8192 and at the default n = 65536 (dense secret h = 192, sparse h = 32)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -44,9 +46,11 @@ def test_bootstrap_limbs_equal_the_oracle_run(logN, batch):
     g.close()
 
 
-@pytest.mark.parametrize("logN", [13, 16])
+@pytest.mark.parametrize("logN", [13] + ([16] if os.environ.get("LSB_TEST_BTP_N16") else []))
 def test_bootstrap_precision(logN):
-    """toy_bootstrap (n = 8192) and bootstrap (n = 65536) of the reference's GPU tests: level 0 -> level 9, >= 10 bits"""
+    """toy_bootstrap (n = 8192) of the reference's GPU tests: level 0 -> level 9, >= 10 bits, and a second run on the cached
+    plaintexts is bit-identical.  (n = 65536 runs through the reference boundary in tests/test_runner_gpu.py
+    [ckks_btp64k_bootstrap]; LSB_TEST_BTP_N16=1 repeats it here at the kernel-level ABI: 17.6 bits, 117 key switches.)"""
     P, o, spec, keys, zs, cts, g, bt = _setup(logN, 9, 1)
     got, st = bt.run(cts)
     again, _ = bt.run(cts)  # second run on the cached plaintexts: deterministic

@@ -329,3 +329,44 @@ def test_linear_transform_parity():
         got = ev.linear(ct, m, n1, float(prm.q[4]))
         assert np.array_equal(got.data, want.data)
         assert np.abs(ev.decode(got, secret) - B.apply(m, z)).max() < 1e-6
+
+
+@pytest.mark.parametrize("params", [R.CKKS_N13, R.BFV_N13], ids=lambda p: p.name)
+@pytest.mark.parametrize("m,with_acc,ringt", [(2, False, False), (5, True, False), (20, False, True), (3, True, True)])
+def test_mac_parity(params, m, with_acc, ringt):
+    """lsb_mac (bind_gpu_cmp_sum / bind_gpu_cmpac_sum, mega_ag_executors_gpu.cu:294-408; reference cases
+    unittests/test_gpu_ckks.cpp:675-705 `ct_pt_mac` m = 2..20) against the node-by-node oracle evaluation: NTT-domain
+    plaintexts (CKKS pt / BFV pt_mul) and pt_ringt, with and without a partial sum, batch of 2."""
+    o = R.Oracle(params)
+    g = _ctx(params)
+    rng = np.random.default_rng(m)
+    lv = params.max_level - 1
+    l = lv + 1
+    bfv = params.scheme == R.SCHEME_BFV
+    q = params.q[:l]
+    rand = lambda lead: np.stack([rng.integers(0, mod, size=lead + (o.N,), dtype=np.uint64) for mod in q], axis=-2)
+    B = 2
+    cts = [rand((B, 2)) for _ in range(m)]
+    if ringt:
+        t = params.t if bfv else 65537
+        pts = [rng.integers(0, t, size=(B, 1, o.N), dtype=np.uint64) for _ in range(m)]
+        pts_ntt = [np.stack([o.ntt_limbs(np.repeat(p[b], l, axis=0)) for b in range(B)]) for p in pts]
+    else:
+        pts = [rand((B,)) for _ in range(m)]
+        pts_ntt = pts
+    acc = rand((B, 2)) if with_acc else None
+    want = np.zeros((B, 2, l, o.N), dtype=np.uint64)
+    for b in range(B):
+        tot = None
+        for i in range(m):
+            x = o.ntt_limbs(cts[i][b]) if bfv else cts[i][b]
+            term = np.zeros_like(x)
+            for p in range(2):
+                for j in range(l):
+                    term[p, j] = ((x[p, j].astype(object) * pts_ntt[i][b][j].astype(object)) % q[j]).astype(np.uint64)
+            tot = term if tot is None else o.add(tot, term)
+        out = o.ntt_limbs(tot, inverse=True) if bfv else tot
+        want[b] = o.add(out, acc[b]) if with_acc else out
+    got = g.mac(cts, pts, ringt=ringt, acc=acc)
+    assert np.array_equal(got, want)
+    g.close()

@@ -251,6 +251,18 @@ class RunnerArm:
         self.GE.runner_lib().lsb_gpu_task_last_stats(self.task, *[C.byref(x) for x in st])
         return tuple(x.value for x in st)
 
+    def host_profile(self):
+        C = self.C
+        L = self.GE.runner_lib()
+        ms = (C.c_double * 6)()
+        L.lsb_gpu_task_host_profile.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        L.lsb_gpu_task_host_profile(self.task, ms)
+        tr = [C.c_longlong() for _ in range(4)]
+        L.lsb_gpu_task_transfer_stats(self.task, *[C.byref(x) for x in tr])
+        d = dict(zip(["wall_ms", "export_ms_sum", "stage_ms_sum", "ring_wait_ms_sum", "d2h_wait_ms_sum", "import_ms_sum"], [round(x, 2) for x in ms]))
+        d.update(dict(zip(["h2d_bytes", "d2h_bytes", "zero_copy_bytes", "key_bytes_cached"], [x.value for x in tr])))
+        return d
+
     def close(self):
         import shutil
         self.h.th_close(self.task)
@@ -370,6 +382,7 @@ def run_ours(args):
                    "path": "create_/bind_/run_fhe_gpu_task (include/lattisense_gpu_runner.h), %d-node mega_ag graph, "
                            "test plug-in EXPORT/IMPORT over host limb buffers" % (3 * B),
                    "runner_stats": {"kernel_launches": st[0], "batched_groups": st[1], "fused_nodes": st[2]},
+                   "host_profile_last_step": arm.host_profile(),
                    "matches_device_path": bool(torch.equal(out_host, out_dev.cpu()))}
         finally:
             arm.close()

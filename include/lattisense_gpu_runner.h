@@ -131,6 +131,28 @@ const char* lsb_gpu_task_last_error(void);
 void lsb_gpu_task_last_stats(fhe_task_handle handle, long long* kernel_launches, long long* batched_groups,
                              long long* fused_nodes);
 
+/* Device-resident key cache across run() calls (the reference uploads every key on every run,
+ * mega_ag_runners/gpu/gpu_abi_bridge_executors.h:213-310): with the cache on, a key HANDLE (the opaque pointer in
+ * CArgument.data) that was passed to an earlier run of this task is neither exported nor uploaded again -- the caller
+ * promises that the handle still holds the same key.  Off by default (or LSB_KEY_CACHE=1 in the environment);
+ * lsb_gpu_task_invalidate_keys drops the cached keys (call it after re-generating keys in place). */
+void lsb_gpu_task_set_key_cache(fhe_task_handle handle, int on);
+void lsb_gpu_task_invalidate_keys(fhe_task_handle handle);
+/* Transfer accounting of the last run: bytes copied host->device and device->host, the part of the former that was
+ * read straight out of the pinned staging memory lent to the EXPORT executor (no second host copy), and key bytes
+ * not uploaded thanks to the key cache. */
+void lsb_gpu_task_transfer_stats(fhe_task_handle handle, long long* h2d_bytes, long long* d2h_bytes, long long* zero_copy_bytes,
+                                 long long* key_bytes_cached);
+
+/* Copy helper for plug-in EXPORT / IMPORT executors: memcpy semantics, streaming (non-temporal) stores for large aligned
+ * blocks.  Limbs handed out by alloc_component while an EXPORT executor runs are pinned staging memory that the CPU never
+ * reads again; filling them with this instead of memcpy removes the read-for-ownership traffic (a third of the copy). */
+void lsb_host_copy(void* dst, const void* src, size_t bytes);
+/* Host-side time of the last run in ms: [0] wall time of run_fhe_gpu_task, then SUMS over the worker threads of
+ * [1] EXPORT executors, [2] staging copies, [3] waiting for pinned-ring space, [4] waiting for a result's D2H copy,
+ * [5] IMPORT executors. */
+void lsb_gpu_task_host_profile(fhe_task_handle handle, double* ms6);
+
 #ifdef __cplusplus
 }
 #endif

@@ -35,3 +35,9 @@ void lsr_stream_copy(void* dst, const void* src, size_t bytes) {
 }
 
 }  // namespace lsr
+
+// Public copy helper for plug-in EXPORT / IMPORT executors (declared in include/lattisense_gpu_runner.h): limbs handed
+// out by alloc_component during an EXPORT are pinned staging memory the CPU never reads again, so filling them with
+// streaming stores saves the read-for-ownership third of the host memory traffic -- and host DRAM bandwidth, not PCIe
+// or the GPU, is what bounds run_fhe_gpu_task end to end (profiles/r02_e2e_host_path.txt).
+extern "C" void lsb_host_copy(void* dst, const void* src, size_t bytes) { lsr::lsr_stream_copy(dst, src, bytes); }

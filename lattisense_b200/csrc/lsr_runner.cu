@@ -33,6 +33,7 @@
 #include "lsb_ops.h"
 #include "lsb_bootstrap_dev.h"
 #include "lsr_graph.h"
+#include "lsr_abi_arena.h"
 
 namespace lsr {
 
@@ -118,6 +119,7 @@ struct PinnedRing {
     void init(size_t bytes) {
         LSB_CUDA(cudaHostAlloc((void**)&base, bytes, cudaHostAllocDefault));
         cap = bytes;
+        lsr::register_pinned_range(base, bytes);  // limbs lent to ABI structs must never reach free() (lsr_abi.cpp)
     }
     void destroy() {
         for (auto& b : busy)
@@ -125,7 +127,10 @@ struct PinnedRing {
         for (auto e : free_events) cudaEventDestroy(e);
         busy.clear();
         free_events.clear();
-        if (base) cudaFreeHost(base);
+        if (base) {
+            lsr::unregister_pinned_range(base);
+            cudaFreeHost(base);
+        }
         base = nullptr;
     }
     cudaEvent_t new_event() {
@@ -214,6 +219,15 @@ struct DeviceRuntime {
     std::unique_ptr<lsb::Context> ctx;
     std::unique_ptr<lsb::Workspace> ws;
     cudaStream_t compute = nullptr, h2d = nullptr, d2h = nullptr;
+    // extra upload streams: object copies alternate over them so that two copy engines keep the link busy across the
+    // per-transfer gaps of 1 MiB objects (LSB_H2D_STREAMS; default 1: measured no gain on cfg2, the path is host-DRAM bound)
+    std::vector<cudaStream_t> h2d_extra;
+    std::atomic<unsigned> h2d_rr{0};
+    cudaStream_t next_h2d() {
+        if (h2d_extra.empty()) return h2d;
+        const unsigned i = h2d_rr.fetch_add(1) % (unsigned)(h2d_extra.size() + 1);
+        return i == 0 ? h2d : h2d_extra[i - 1];
+    }
     std::mutex mu;  // serialises enqueues on the copy streams (worker threads issue copies)
     PinnedRing up, down;
     // device pointer tables of batched launches: pinned host mirror + device arena, both rings
@@ -229,6 +243,7 @@ struct DeviceRuntime {
         cudaSetDevice(device);
         if (compute) cudaStreamSynchronize(compute);
         if (h2d) cudaStreamSynchronize(h2d);
+        for (auto st : h2d_extra) cudaStreamSynchronize(st);
         if (d2h) cudaStreamSynchronize(d2h);
         up.destroy();
         down.destroy();
@@ -240,6 +255,7 @@ struct DeviceRuntime {
         ctx.reset();
         if (compute) cudaStreamDestroy(compute);
         if (h2d) cudaStreamDestroy(h2d);
+        for (auto st : h2d_extra) cudaStreamDestroy(st);
         if (d2h) cudaStreamDestroy(d2h);
     }
 };
@@ -268,6 +284,11 @@ static std::unique_ptr<DeviceRuntime> make_device_runtime(int device, const Task
     rt->ws.reset(new lsb::Workspace(device));
     LSB_CUDA(cudaStreamCreateWithFlags(&rt->compute, cudaStreamNonBlocking));
     LSB_CUDA(cudaStreamCreateWithFlags(&rt->h2d, cudaStreamNonBlocking));
+    for (size_t i = 1; i < std::max<size_t>(1, env_mb("LSB_H2D_STREAMS", 1)); i++) {
+        cudaStream_t st;
+        LSB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        rt->h2d_extra.push_back(st);
+    }
     LSB_CUDA(cudaStreamCreateWithFlags(&rt->d2h, cudaStreamNonBlocking));
     rt->up.init(env_mb("LSB_STAGING_MB", 512) << 20);
     rt->down.init(env_mb("LSB_STAGING_MB", 512) << 20);
@@ -609,6 +630,18 @@ struct GpuTask {
     FrontendContextFactory ctx_factory;
     std::mutex run_mu;  // one run at a time per handle (like the reference: FheTask::input_args is reused)
     long long stat_launches = 0, stat_groups = 0, stat_fused = 0;
+    // transfer accounting of the last run: bytes copied host->device / device->host, of which read straight out of the
+    // pinned ring the EXPORT executor wrote into (no staging copy), and key bytes NOT uploaded thanks to the key cache
+    std::atomic<long long> stat_h2d{0}, stat_d2h{0}, stat_zero_copy{0}, stat_key_cached{0};
+    // host-side time of the last run, summed over worker threads (ns): EXPORT executors, staging copies, waiting for ring
+    // space, waiting for a result's D2H, IMPORT executors; and the wall time of the run
+    std::atomic<long long> ns_export{0}, ns_stage{0}, ns_ring_wait{0}, ns_d2h_wait{0}, ns_import{0}, ns_wall{0};
+    // device-resident key cache across run() calls (the reference re-uploads every key on every run,
+    // gpu_abi_bridge_executors.h:213-310): opt-in (lsb_gpu_task_set_key_cache / LSB_KEY_CACHE=1) because it assumes that
+    // a key HANDLE that is passed again still holds the same key; lsb_gpu_task_invalidate_keys drops it
+    bool key_cache_on = false;
+    std::mutex key_mu;
+    std::map<std::pair<const void*, NodeIndex>, std::any> key_cache;  // (caller's key handle, LOAD output datum) -> DatumPtr
 
     DeviceRuntime* runtime(int device, int ordinal = 0) {
         const std::pair<int, int> key(device, ordinal);
@@ -619,6 +652,9 @@ struct GpuTask {
 };
 
 static thread_local std::string g_runner_error;
+static inline long long now_ns() {
+    return std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
 
 // ---------------------------------------------------------------------------------------------
 // one run
@@ -650,6 +686,55 @@ struct RunState {
     std::string error;
     std::atomic<int64_t> last_progress_ns{0};
     std::atomic<long long> groups{0};
+
+    // Result drains: a D2H copy is awaited by ONE helper thread (copies on the store stream finish in order), and only
+    // then is the IMPORT work handed to the pool -- pool threads never block on the GPU (measured on cfg2 x1024: 15
+    // threads spent 16 ms each of a 67 ms call inside cudaEventSynchronize).
+    struct PendingDrain {
+        cudaEvent_t ev;
+        int device;
+        int priority;
+        std::function<void()> work;
+    };
+    std::deque<PendingDrain> drains;
+    std::mutex drain_mu;
+    std::condition_variable drain_cv;
+    bool drain_stop = false;
+    std::thread drainer;
+    void drain_loop() {
+        for (;;) {
+            PendingDrain d;
+            {
+                std::unique_lock<std::mutex> lk(drain_mu);
+                drain_cv.wait(lk, [&] { return drain_stop || !drains.empty(); });
+                if (drains.empty()) return;
+                d = std::move(drains.front());
+                drains.pop_front();
+            }
+            cudaSetDevice(d.device);
+            const long long t0 = now_ns();
+            cudaEventSynchronize(d.ev);  // an error surfaces in the continuation's own CUDA calls
+            task.ns_d2h_wait += now_ns() - t0;
+            pool.submit(d.priority, std::move(d.work));
+        }
+    }
+    void submit_drain(PendingDrain d) {
+        {
+            std::lock_guard<std::mutex> lk(drain_mu);
+            if (!drainer.joinable()) drainer = std::thread([this] { drain_loop(); });
+            drains.push_back(std::move(d));
+        }
+        drain_cv.notify_one();
+    }
+    void stop_drainer() {
+        {
+            std::lock_guard<std::mutex> lk(drain_mu);
+            drain_stop = true;
+        }
+        drain_cv.notify_all();
+        if (drainer.joinable()) drainer.join();
+    }
+    ~RunState() { stop_drainer(); }
 
     RunState(GpuTask& t, WorkerPool& wp, progress_callback_t cb, void* ud)
         : task(t), g(*t.graph), plan(t.plan), pool(wp), progress_cb(cb), user_data(ud) {}
@@ -784,6 +869,21 @@ void collect_ksk(const CKeySwitchKey& k, LimbList& out) {
 }
 }  // namespace
 
+// words of the object a LOAD unit is about to receive, from the datum's metadata (an estimate: the arena falls back to
+// malloc when the executor allocates more, and the staging copy takes over)
+static size_t expected_words(const TaskGraph& g, const DatumNode* d) {
+    if (!d->fhe_prop.has_value()) return 0;
+    const size_t n = (size_t)g.param.n, l = (size_t)d->fhe_prop->level + 1, k = g.param.p.size();
+    switch (d->datum_type) {
+        case TYPE_CIPHERTEXT: return (size_t)(d->fhe_prop->degree + 1) * l * n;
+        case TYPE_PLAINTEXT: return (d->fhe_prop->p.has_value() && d->fhe_prop->p->is_ringt) ? n : l * n;
+        case TYPE_RELIN_KEY:
+        case TYPE_GALOIS_KEY:
+        case TYPE_SWITCH_KEY: return k ? ((l + k - 1) / k) * 2 * (l + k) * n : 0;
+        default: return 0;
+    }
+}
+
 void RunState::run_load_unit(const Unit& u) {
     const ComputeNode& node = *u.nodes.back();
     std::any output;
@@ -792,14 +892,73 @@ void RunState::run_load_unit(const Unit& u) {
         const DatumNode* src = node.input_nodes[0];
         LSB_CHECK(src->fhe_prop.has_value(), "Input node missing FHE properties");
         auto in = gather_inputs(u);
+        // ---- device-resident key cache: a key handle seen before on this task is not exported or uploaded again ----
+        const bool cacheable = task.key_cache_on && is_key_type(src->datum_type) && u.ext_inputs.size() == 1 && u.ext_inputs[0]->is_input;
+        std::pair<const void*, NodeIndex> cache_key{nullptr, u.output->index};
+        if (cacheable) {
+            if (auto* hp = std::any_cast<std::shared_ptr<void>>(&in.at(u.ext_inputs[0]->index))) cache_key.first = hp->get();
+            if (cache_key.first) {
+                std::lock_guard<std::mutex> lk(task.key_mu);
+                auto it = task.key_cache.find(cache_key);
+                if (it != task.key_cache.end()) {
+                    output = it->second;
+                    task.stat_key_cached += (long long)expected_words(g, src) * 8;
+                }
+            }
+            if (output.has_value()) {
+                unit_done(u, std::move(output), true);
+                return;
+            }
+        }
+        // ---- which device slots want this object ----
+        const int my_slot = slot_of(u);
+        std::vector<char> wanted(slots.size(), my_slot < 0 ? 0 : 1);
+        if (my_slot < 0) {  // a replicated object (key, plaintext) goes to every device that runs one of its consumers
+            auto cons = plan.consumers.find(u.output->index);
+            if (cons != plan.consumers.end())
+                for (int v : cons->second) {
+                    const int cs = slot_of(plan.units[v]);
+                    if (cs >= 0) wanted[cs] = 1;
+                    else std::fill(wanted.begin(), wanted.end(), 1);
+                }
+        }
+        int owner = my_slot;
+        for (int s2 = 0; owner < 0 && s2 < (int)slots.size(); s2++)
+            if (wanted[s2]) owner = s2;
+        // ---- EXPORT_TO_ABI fused into this unit: run the bound executor here, lending it pinned staging memory ----
         std::any exported;
+        lsr::ExportArena arena;
+        uint64_t arena_ticket = 0;
+        const size_t want_words = expected_words(g, src);
+        static const bool zero_copy = [] {
+            const char* e = getenv("LSB_EXPORT_ZERO_COPY");
+            return !(e && atoi(e) == 0);
+        }();
         if (u.nodes.size() == 2) {
-            // fused EXPORT_TO_ABI: run the bound executor here, on the thread that stages its result
             const ComputeNode& ex = *u.nodes[0];
             if (!ex.executor) throw std::runtime_error("lsb runner: no executor bound for node '" + ex.id + "'");
             ExecutionContext ctx;
             ctx.context = frontend_ctx;
-            ex.executor(ctx, in, exported, ex);
+            const bool lend = zero_copy && owner >= 0 && want_words > 0 && want_words * 8 <= slots[owner]->up.cap / 2;
+            if (lend) {
+                const long long t0 = now_ns();
+                arena.base = slots[owner]->up.acquire(want_words * 8, &arena_ticket);
+                task.ns_ring_wait += now_ns() - t0;
+                arena.cap = want_words * 8;
+                lsr::export_arena_begin(&arena);
+            }
+            const long long t_ex = now_ns();
+            try {
+                ex.executor(ctx, in, exported, ex);
+                task.ns_export += now_ns() - t_ex;
+            } catch (...) {
+                if (lend) {
+                    lsr::export_arena_end();
+                    slots[owner]->up.release(arena_ticket);
+                }
+                throw;
+            }
+            if (lend) lsr::export_arena_end();
         }
         const std::any& cs = u.nodes.size() == 2 ? exported : in.at(src->index);
         LimbList ll;
@@ -853,47 +1012,68 @@ void RunState::run_load_unit(const Unit& u) {
         }
         LSB_CHECK(ll.n == g.param.n, "lsb runner: ring degree of '" + src->id + "' does not match the task parameter");
         const size_t words = ll.limbs.size() * (size_t)ll.n;
+        // did the executor fill the lent region limb after limb, in the order the device layout wants?
+        bool in_place = arena.base && !arena.overflow && arena.used == words * 8;
+        for (size_t i = 0; in_place && i < ll.limbs.size(); i++)
+            in_place = (const uint8_t*)ll.limbs[i] == arena.base + i * (size_t)ll.n * 8;
         DatumPtr datum = std::make_shared<DeviceDatum>();
         datum->on.resize(slots.size());
-        const int my_slot = slot_of(u);
-        // a replicated object (key, plaintext) goes to every device that runs one of its consumers
-        std::vector<char> wanted(slots.size(), my_slot < 0 ? 0 : 1);
-        if (my_slot < 0) {
-            auto cons = plan.consumers.find(u.output->index);
-            if (cons != plan.consumers.end())
-                for (int v : cons->second) {
-                    const int cs = slot_of(plan.units[v]);
-                    if (cs >= 0) wanted[cs] = 1;
-                    else std::fill(wanted.begin(), wanted.end(), 1);
-                }
-        }
-        bool first = true;
         for (int s = 0; s < (int)slots.size(); s++) {
             if (!wanted[s] || (my_slot >= 0 && s != my_slot)) continue;
             DeviceRuntime* rt = slots[s];
             LSB_CUDA(cudaSetDevice(rt->device));
             uint64_t ticket = 0;
-            uint8_t* stage = rt->up.acquire(words * 8, &ticket);
-            for (size_t i = 0; i < ll.limbs.size(); i++) lsr_stream_copy(stage + i * (size_t)ll.n * 8, ll.limbs[i], (size_t)ll.n * 8);
+            uint8_t* stage = nullptr;
+            if (s == owner && arena.base && (in_place || (arena.used == 0 && words * 8 <= arena.cap))) {
+                // the lent region IS the staging buffer: already filled (zero copy), or untouched and reused for the copy
+                stage = arena.base;
+                ticket = arena_ticket;
+                arena.base = nullptr;
+                if (in_place) {
+                    task.stat_zero_copy += (long long)words * 8;
+                } else {
+                    const long long t0 = now_ns();
+                    for (size_t i = 0; i < ll.limbs.size(); i++) lsr_stream_copy(stage + i * (size_t)ll.n * 8, ll.limbs[i], (size_t)ll.n * 8);
+                    task.ns_stage += now_ns() - t0;
+                }
+            } else {
+                long long t0 = now_ns();
+                stage = rt->up.acquire(words * 8, &ticket);
+                task.ns_ring_wait += now_ns() - t0;
+                t0 = now_ns();
+                for (size_t i = 0; i < ll.limbs.size(); i++) lsr_stream_copy(stage + i * (size_t)ll.n * 8, ll.limbs[i], (size_t)ll.n * 8);
+                task.ns_stage += now_ns() - t0;
+            }
             cudaEvent_t ring_ev = rt->up.new_event();
             DevObjPtr obj;
             {
                 std::lock_guard<std::mutex> lk(rt->mu);
-                obj = alloc_device_object(rt, words, rt->h2d);
-                LSB_CUDA(cudaMemcpyAsync(obj->ptr, stage, words * 8, cudaMemcpyHostToDevice, rt->h2d));
-                LSB_CUDA(cudaEventRecord(ring_ev, rt->h2d));
+                cudaStream_t up = rt->next_h2d();
+                obj = alloc_device_object(rt, words, up);
+                LSB_CUDA(cudaMemcpyAsync(obj->ptr, stage, words * 8, cudaMemcpyHostToDevice, up));
+                LSB_CUDA(cudaEventRecord(ring_ev, up));
                 LSB_CUDA(cudaEventCreateWithFlags(&obj->ready, cudaEventDisableTiming));
-                LSB_CUDA(cudaEventRecord(obj->ready, rt->h2d));
+                LSB_CUDA(cudaEventRecord(obj->ready, up));
             }
             rt->up.commit(ticket, ring_ev);
+            task.stat_h2d += (long long)words * 8;
             obj->level = ll.level;
             obj->npoly = ll.npoly;
             obj->limbs = ll.limbs_per_poly;
             datum->on[s] = obj;
-            first = false;
         }
-        (void)first;
+        if (arena.base) {
+            // lent region not used as staging (mismatching layout): its limbs stay valid until the exported struct dies
+            // with `keepalive` at the end of this scope, then the region goes back to the ring
+            keepalive.reset();
+            exported.reset();
+            slots[owner]->up.release(arena_ticket);
+        }
         output = datum;
+        if (cacheable && cache_key.first) {
+            std::lock_guard<std::mutex> lk(task.key_mu);
+            task.key_cache[cache_key] = datum;
+        }
     } catch (const std::exception& e) {
         if (std::string(e.what()) != "cancelled") fail("node '" + node.id + "': " + e.what());
     }
@@ -926,6 +1106,7 @@ void RunState::start_store_unit(const Unit& u) {
             LSB_CUDA(cudaStreamWaitEvent(rt->d2h, done_ev, 0));
             if (obj->ready) LSB_CUDA(cudaStreamWaitEvent(rt->d2h, obj->ready, 0));
             LSB_CUDA(cudaMemcpyAsync(stage, obj->ptr, obj->words * 8, cudaMemcpyDeviceToHost, rt->d2h));
+            task.stat_d2h += (long long)obj->words * 8;
             LSB_CUDA(cudaEventRecord(done_ev, rt->d2h));
         }
         {
@@ -934,12 +1115,22 @@ void RunState::start_store_unit(const Unit& u) {
         }
         const Unit* up = &u;
         // results drain ahead of further input staging
-        pool.submit(kDrainPriority + u.priority, [this, up, obj, rt, stage, ticket, done_ev] {
+        PendingDrain pd;
+        pd.ev = done_ev;
+        pd.device = rt->device;
+        pd.priority = kDrainPriority + u.priority;
+        pd.work = [this, up, obj, rt, stage, ticket, done_ev] {
             std::any output;
             const int n = g.param.n;
             try {
                 LSB_CUDA(cudaSetDevice(rt->device));
-                LSB_CUDA(cudaEventSynchronize(done_ev));
+                LSB_CUDA(cudaEventSynchronize(done_ev));  // already complete (awaited by the drain thread)
+                const long long t_imp = now_ns();
+                struct ImportTimer {
+                    GpuTask& t;
+                    long long t0;
+                    ~ImportTimer() { t.ns_import += now_ns() - t0; }
+                } import_timer{task, t_imp};
                 if (up->nodes.size() == 2) {
                     // fused IMPORT_FROM_ABI: hand the bound executor a CCiphertext whose limbs ARE the pinned staging
                     // region (valid for the duration of the call; the struct is owned by the runner, wrapper.h ownership
@@ -989,7 +1180,8 @@ void RunState::start_store_unit(const Unit& u) {
             rt->down.release(ticket);  // the staging region is free again
             cudaEventDestroy(done_ev);
             unit_done(*up, std::move(output), true);
-        });
+        };
+        submit_drain(std::move(pd));
         return;
     } catch (const std::exception& e) {
         if (std::string(e.what()) != "cancelled") fail("node '" + node.id + "': " + e.what());
@@ -1569,14 +1761,20 @@ static int run_task(GpuTask& task, CArgument* input_args, uint64_t n_in, CArgume
     TaskGraph& g = *task.graph;
     std::vector<int> devs = task.devices.empty() ? std::vector<int>{gpu_device} : task.devices;
     const int hw = (int)std::thread::hardware_concurrency();
-    // worker threads: min(16, cores) - 1 like the reference's pool cap (cpu_wrapper.cpp:57), shared fairly when several
-    // ranks run on one node (torchrun exports LOCAL_WORLD_SIZE); LSB_HOST_THREADS overrides
+    // worker threads: the copies they make are bound by host DRAM bandwidth, not by cores -- measured on a 16-core B200
+    // host (cfg2 x1024 through run_fhe_gpu_task, profiles/r02_e2e_host_path.txt): 8 threads 62 ms, 12 threads 65 ms,
+    // 15 threads 73 ms per call -- so the pool is capped at 8 (the reference's pool cap is min(32, cores),
+    // cpu_wrapper.cpp:57) and shared fairly when several ranks run on one node (torchrun exports LOCAL_WORLD_SIZE);
+    // LSB_HOST_THREADS overrides
     int share = hw > 0 ? hw : 4;
     if (const char* lw = getenv("LOCAL_WORLD_SIZE")) share = std::max(2, share / std::max(1, atoi(lw)));
-    int nthreads = std::max(2, std::min(16, share) - 1);
+    int nthreads = std::max(2, std::min(9, share) - 1);
     if (const char* ht = getenv("LSB_HOST_THREADS")) nthreads = std::max(1, atoi(ht));
     static WorkerPool pool(nthreads);  // shared by all tasks of the process
     RunState rs(task, pool, cb, ud);
+    task.stat_h2d = task.stat_d2h = task.stat_zero_copy = task.stat_key_cached = 0;
+    task.ns_export = task.ns_stage = task.ns_ring_wait = task.ns_d2h_wait = task.ns_import = 0;
+    const long long t_run0 = now_ns();
     long long launches0 = 0;
     {
         std::map<int, int> seen;
@@ -1663,11 +1861,13 @@ static int run_task(GpuTask& task, CArgument* input_args, uint64_t n_in, CArgume
         LSB_CUDA(cudaSetDevice(rt->device));
         LSB_CUDA(cudaStreamSynchronize(rt->compute));
         LSB_CUDA(cudaStreamSynchronize(rt->h2d));
+        for (auto st : rt->h2d_extra) LSB_CUDA(cudaStreamSynchronize(st));
         LSB_CUDA(cudaStreamSynchronize(rt->d2h));
     }
     rs.avail.clear();
     long long launches1 = 0;
     for (DeviceRuntime* rt : rs.slots) launches1 += rt->ctx->prof.launches.load();
+    task.ns_wall = now_ns() - t_run0;
     task.stat_launches = launches1 - launches0;
     task.stat_groups = rs.groups;
     task.stat_fused = task.plan.fused_nodes;
@@ -1718,6 +1918,7 @@ fhe_task_handle create_fhe_gpu_task(const char* project_path) {
     if (!project_path) throw std::runtime_error("create_fhe_gpu_task: null project path");
     std::unique_ptr<GpuTask> t(new GpuTask());
     t->graph.reset(lsr::TaskGraph::load(std::string(project_path) + "/mega_ag.json"));
+    if (const char* kc = getenv("LSB_KEY_CACHE")) t->key_cache_on = atoi(kc) != 0;
     const char* nofuse = getenv("LSB_NO_FUSE");
     const char* nohost = getenv("LSB_NO_HOST_FUSE");
     t->plan = lsr::build_plan(*t->graph, !(nofuse && atoi(nofuse) != 0), !(nohost && atoi(nohost) != 0));
@@ -1762,6 +1963,46 @@ void lsb_gpu_task_set_devices(fhe_task_handle handle, const int* devices, int n_
     if (!t) return;
     std::lock_guard<std::mutex> lk(t->run_mu);
     t->devices.assign(devices, devices + (n_devices > 0 ? n_devices : 0));
+    std::lock_guard<std::mutex> lk2(t->key_mu);
+    t->key_cache.clear();  // cached keys live on the device slots of the previous configuration
+}
+
+void lsb_gpu_task_set_key_cache(fhe_task_handle handle, int on) {
+    GpuTask* t = reinterpret_cast<GpuTask*>(handle);
+    if (!t) return;
+    std::lock_guard<std::mutex> lk(t->run_mu);
+    t->key_cache_on = on != 0;
+    if (!on) {
+        std::lock_guard<std::mutex> lk2(t->key_mu);
+        t->key_cache.clear();
+    }
+}
+void lsb_gpu_task_invalidate_keys(fhe_task_handle handle) {
+    GpuTask* t = reinterpret_cast<GpuTask*>(handle);
+    if (!t) return;
+    std::lock_guard<std::mutex> lk(t->run_mu);
+    std::lock_guard<std::mutex> lk2(t->key_mu);
+    t->key_cache.clear();
+}
+void lsb_gpu_task_transfer_stats(fhe_task_handle handle, long long* h2d_bytes, long long* d2h_bytes, long long* zero_copy_bytes,
+                                 long long* key_bytes_cached) {
+    GpuTask* t = reinterpret_cast<GpuTask*>(handle);
+    if (!t) return;
+    if (h2d_bytes) *h2d_bytes = t->stat_h2d.load();
+    if (d2h_bytes) *d2h_bytes = t->stat_d2h.load();
+    if (zero_copy_bytes) *zero_copy_bytes = t->stat_zero_copy.load();
+    if (key_bytes_cached) *key_bytes_cached = t->stat_key_cached.load();
+}
+
+void lsb_gpu_task_host_profile(fhe_task_handle handle, double* ms6) {
+    GpuTask* t = reinterpret_cast<GpuTask*>(handle);
+    if (!t || !ms6) return;
+    ms6[0] = 1e-6 * (double)t->ns_wall.load();
+    ms6[1] = 1e-6 * (double)t->ns_export.load();
+    ms6[2] = 1e-6 * (double)t->ns_stage.load();
+    ms6[3] = 1e-6 * (double)t->ns_ring_wait.load();
+    ms6[4] = 1e-6 * (double)t->ns_d2h_wait.load();
+    ms6[5] = 1e-6 * (double)t->ns_import.load();
 }
 
 void lsb_gpu_task_last_stats(fhe_task_handle handle, long long* kernel_launches, long long* batched_groups, long long* fused_nodes) {

@@ -45,7 +45,7 @@ THandle* handle_of(const DatumNode* d, const std::any& a, std::shared_ptr<THandl
 }
 
 void fill_poly(CPolynomial& p, const uint64_t* src, int n) {
-    for (int i = 0; i < p.n_component; i++) std::memcpy(p.components[i].data, src + (size_t)i * n, (size_t)n * 8);
+    for (int i = 0; i < p.n_component; i++) lsb_host_copy(p.components[i].data, src + (size_t)i * n, (size_t)n * 8);
 }
 
 // key handle at key level KL -> CKeySwitchKey at `level` (plug-in/lattigo/acc/c_struct_import_export.go:83-135):
@@ -70,7 +70,7 @@ void export_ksk(const THandle* h, int level, CKeySwitchKey* out) {
             for (int t = 0; t < dst_limbs; t++) {
                 const int s = t <= level ? t : KL + 1 + (t - level - 1);
                 alloc_component(&poly.components[t], n);
-                std::memcpy(poly.components[t].data, base + (size_t)s * n, (size_t)n * 8);
+                lsb_host_copy(poly.components[t].data, base + (size_t)s * n, (size_t)n * 8);
             }
         }
     }
@@ -148,7 +148,7 @@ void copy_ct(THandle* dst, const CCiphertext* c) {
         throw std::runtime_error("harness: output handle shape does not match the produced ciphertext");
     for (int p = 0; p <= c->degree; p++)
         for (int i = 0; i <= c->level; i++)
-            std::memcpy(dst->data + ((size_t)p * (c->level + 1) + i) * dst->n, c->polys[p].components[i].data, (size_t)dst->n * 8);
+            lsb_host_copy(dst->data + ((size_t)p * (c->level + 1) + i) * dst->n, c->polys[p].components[i].data, (size_t)dst->n * 8);
 }
 
 ExecutorFunc make_import() {

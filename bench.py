@@ -467,6 +467,41 @@ def run_ours(args):
             c16.h, l25 - 1, c3.data_ptr(), rk.data_ptr(), l25 - 1, o2.data_ptr(), B25, stream)), B25)
         del c3, rk, o2
         c16.close()
+        # CKKS bootstrapping N=2^16 (configs[4]): one `bootstrap` node = level 0 -> level 9 on the 25 Q + 5 P chain; random
+        # residues for ciphertext and keys (the op sequence is data-independent; parity / precision: tests/test_bootstrap_gpu.py,
+        # tests/test_runner_gpu.py[ckks_btp64k_bootstrap])
+        try:
+            import btp_ref as BT
+            spec = BT.BtpSpec(P16)
+            c16 = L.Context(P16.scheme, P16.logN, P16.q, P16.p, 0, device=local)
+            c16.stream = stream
+            bt = L.Bootstrapper(c16, list(spec.ints()), list(spec.doubles()))
+            rots = bt.rotations()
+            top = len(P16.q) - 1
+            # 4 x 150 MiB stand in for the 51 keys (same traffic per use)
+            key_pool = [limbs((P16.beta(top), 2), P16.q + P16.p, P16.N) for _ in range(4)]
+            gals = [R.galois_for_col_step(P16.N, r) for r in rots] + [R.galois_for_row(P16.N)]
+            garr = np.array(gals, dtype=np.uint64)
+            gptr = (C.c_void_p * len(gals))(*[key_pool[i % 4].data_ptr() for i in range(len(gals))])
+            dts = limbs((1, 2), [P16.q[0]] + P16.p, P16.N)
+            for Bb_ in (1, 4):
+                ct0 = limbs((Bb_, 2), P16.q[:1], P16.N)
+                outb = torch.empty((Bb_, 2, spec.out_level + 1, P16.N), dtype=torch.int64, device=dev)
+                stats = (C.c_longlong * 5)()
+                run = lambda: L._check(lib.lsb_bootstrap_run(bt.h, ct0.data_ptr(), key_pool[0].data_ptr(), top, garr.ctypes.data_as(L.u64p),
+                                                             gptr, len(gals), dts.data_ptr(), key_pool[1].data_ptr(), outb.data_ptr(), Bb_,
+                                                             stream, stats))
+                run()  # encodes the CoeffsToSlots / SlotsToCoeffs plaintexts once
+                torch.cuda.synchronize()
+                ms_b = timed(run, 2) / 2
+                secondary["ckks_bootstrap_n65536_per_s_batch%d" % Bb_] = Bb_ / (ms_b / 1e3)
+                secondary["ckks_bootstrap_n65536_ms_batch%d" % Bb_] = ms_b
+            secondary["ckks_bootstrap_key_switches"] = int(stats[1])
+            secondary["ckks_bootstrap_ops"] = {"rotations": int(stats[0]), "ct_x_ct": int(stats[2]), "rescales": int(stats[3]), "ct_x_pt": int(stats[4])}
+            bt.close()
+            c16.close()
+        except Exception as ex:  # never lose the headline line to a side measurement
+            secondary["ckks_bootstrap_error"] = str(ex)[:200]
         secondary["note"] = ("device-resident, CUDA events, batches 1024 / 256 / 64 / 8; random residues (throughput does "
                              "not depend on values)")
 

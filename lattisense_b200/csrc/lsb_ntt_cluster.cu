@@ -22,6 +22,9 @@
 #include "lsb_ntt_cluster_core.h"
 #include "lsb_ntt_persist_core.h"
 
+#ifndef LSB_FIN_PREFETCH
+#define LSB_FIN_PREFETCH 1
+#endif
 #ifndef LSB_CL_RMAJOR
 #define LSB_CL_RMAJOR 0
 #endif
@@ -132,6 +135,20 @@ __device__ __forceinline__ void ntt_cluster_body(const NttClArgs& a, u64* sm) {
     cg::cluster_group cluster = cg::this_cluster();
 
     if (!INV) {
+#if LSB_FIN_PREFETCH
+        if constexpr (FIN) {
+            // the finish epilogue reads this CTA's slice of `a` (and of the addend) only after every round: start those
+            // HBM reads now, into L2, so that the epilogue's loads find them there (no registers, no shared memory)
+            const int f = a.map.out_slot[r];
+            const FinishMap& fm = *a.fm;
+            const char* pa = reinterpret_cast<const char*>(a.fa.at(b) + (size_t)fm.a_slot[f] * N + (size_t)rank * TILE);
+            for (int c = tid * 128; c < TILE * 8; c += NT * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(pa + c));
+            if (a.has_add && fm.add_slot[f] != 0xFF) {
+                const char* pz = reinterpret_cast<const char*>(a.fadd.at(b) + (size_t)fm.add_slot[f] * N + (size_t)rank * TILE);
+                for (int c = tid * 128; c < TILE * 8; c += NT * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(pz + c));
+            }
+        }
+#endif
         // ---- cross round: stages 0..3 on words g + k*BS, outputs scattered to the owners of block k ----
         u64* peer[CL];
 #pragma unroll

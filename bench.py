@@ -505,6 +505,17 @@ def run_ours(args):
         secondary["note"] = ("device-resident, CUDA events, batches 1024 / 256 / 64 / 8; random residues (throughput does "
                              "not depend on values)")
 
+    # multi-GPU only: the path's one exchange step -- the limb-sharded key-switch for N=2^16 through
+    # the library's C++ NCCL driver (lsb_ks_shard_*), batch 16, every rank's limbs checked against the oracle
+    limb = None
+    if world > 1 and not args.no_secondary:
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import ks_shard_nccl_run as KS
+            from lattisense_b200.dist import Ranks
+            limb = KS.measure(16, 24, 16, 10, check=True, rk=Ranks())
+        except Exception as ex:
+            limb = {"error": str(ex)[:300]}
     if rank != 0:
         return
     cores = len(os.sched_getaffinity(0))
@@ -544,6 +555,7 @@ def run_ours(args):
                      "standalone_ntt_gbs": ntt_alone, "standalone_frac": ntt_alone / peak},
         "kernel_ms_per_step": {k: v[0] for k, v in prof.items()},
         "secondary": secondary,
+        "limb_sharded_keyswitch": limb,
         "cpu_baseline": cpu,
     }
     print(json.dumps(line), flush=True)

@@ -170,6 +170,23 @@ int lsb_ks_shard_end(lsb_context_t ctx, int level, int world, int rank, const ui
                      const uint64_t* d_acc_own, const uint64_t* d_addend_own /* may be NULL */, uint64_t* d_out_own,
                      int batch, void* stream);
 
+/* ---- the same key-switch driven entirely from C/C++: one handle per rank owns the NCCL communicator, the exchange
+ * buffers and a CUDA graph of the whole sequence (phase 1, all-gather, phase 2, all-gather, phase 3), batched over
+ * `batch` ciphertexts.  NCCL is loaded at run time (libnccl.so.2).  Rank 0 calls lsb_nccl_unique_id and distributes the
+ * 128 bytes to the other ranks by any means (torch.distributed broadcast, MPI, a file); every rank then creates its
+ * handle with the same id (collective call).  Buffers per rank, densely packed per batch item:
+ *   d_c_own_ntt [batch][nq_own][N], d_evk_own [beta][2][nq_own+np_own][N] (shared by the batch),
+ *   d_addend_own (may be NULL) / d_out_own [batch][2][nq_own][N].
+ * Every limb equals the single-GPU key-switch's bit for bit.  world = 1 degenerates to the single-GPU key-switch. */
+typedef struct lsb_ks_shard_st* lsb_ks_shard_t;
+int lsb_nccl_unique_id(void* id128);
+lsb_ks_shard_t lsb_ks_shard_create(lsb_context_t ctx, int level, int world, int rank, const void* nccl_unique_id128, int max_batch);
+void lsb_ks_shard_destroy(lsb_ks_shard_t h);
+int lsb_ks_shard_run(lsb_ks_shard_t h, const uint64_t* d_c_own_ntt, const uint64_t* d_evk_own, const uint64_t* d_addend_own,
+                     uint64_t* d_out_own, int batch, void* stream);
+long long lsb_ks_shard_all_gather_bytes(lsb_ks_shard_t h); /* bytes this rank contributed to the two all-gathers of the last run */
+const char* lsb_ks_shard_last_error(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -83,6 +83,14 @@ def lib():
     L.lsb_bootstrap_destroy.argtypes = [vp]
     L.lsb_bootstrap_rotations.argtypes = [vp, i32p, ci]
     L.lsb_bootstrap_run.argtypes = [vp, vp, vp, ci, u64p, C.POINTER(C.c_void_p), ci, vp, vp, vp, ci, vp, C.POINTER(C.c_longlong)]
+    L.lsb_nccl_unique_id.argtypes = [vp]
+    L.lsb_ks_shard_create.restype = C.c_void_p
+    L.lsb_ks_shard_create.argtypes = [vp, ci, ci, ci, vp, ci]
+    L.lsb_ks_shard_destroy.argtypes = [vp]
+    L.lsb_ks_shard_run.argtypes = [vp, vp, vp, vp, vp, ci, vp]
+    L.lsb_ks_shard_all_gather_bytes.restype = C.c_longlong
+    L.lsb_ks_shard_all_gather_bytes.argtypes = [vp]
+    L.lsb_ks_shard_last_error.restype = C.c_char_p
     L.lsb_launch_count.restype = C.c_longlong
     L.lsb_launch_count.argtypes = [vp]
     L.lsb_profile_enable.argtypes = [vp, ci]

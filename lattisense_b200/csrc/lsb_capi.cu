@@ -15,6 +15,11 @@ struct lsb_context_st {
 
 static thread_local std::string g_err;
 
+Context& lsb_context_ref(lsb_context_t h) {  // for the other translation units behind lsb200.h (lsb_shard_nccl.cu)
+    LSB_CHECK(h && h->c, "lsb: null context");
+    return *h->c;
+}
+
 #define LSB_API_BEGIN \
     g_err.clear();    \
     try {

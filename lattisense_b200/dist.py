@@ -210,3 +210,50 @@ class ShardedKeySwitch:
         self.gather(self.accP_own, self.accP_all)
         self.end(addend_own, out)
         return out[:, :self.nq_own]
+
+
+class NcclShardedKeySwitch:
+    """Binding of the C++ driver of the limb-sharded key-switch (lsb_ks_shard_create / _run, csrc/lsb_shard_nccl.cu): the
+    library owns the NCCL communicator, the exchange buffers and the CUDA graph; this class only distributes the NCCL
+    unique id over torch.distributed (rendezvous plumbing) and passes device pointers."""
+
+    def __init__(self, ctx, level, world, rank, max_batch=1, device=None):
+        import ctypes as C
+        import lattisense_b200 as L
+        self.L, self.C, self.ctx = L, C, ctx
+        self.level, self.world, self.rank, self.max_batch = level, world, rank, max_batch
+        lay = shard_layout(level, ctx.k, world, rank)
+        self.own_q, self.own_p = lay["own_q"], lay["own_p"]
+        self.nq_own, self.np_own = len(self.own_q), len(self.own_p)
+        self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+        idbuf = (C.c_uint8 * 128)()
+        if rank == 0:
+            L._check(L.lib().lsb_nccl_unique_id(idbuf))
+        if world > 1:
+            t = torch.tensor(list(idbuf), dtype=torch.uint8, device=self.device)
+            dist.broadcast(t, src=0)
+            idbuf = (C.c_uint8 * 128)(*t.cpu().tolist())
+        self.h = L.lib().lsb_ks_shard_create(ctx.h, level, world, rank, idbuf, max_batch)
+        if not self.h:
+            raise L.LsbError(L.lib().lsb_ks_shard_last_error().decode())
+
+    def run(self, c_own_ntt, evk_own, addend_own=None, out=None, stream=None):
+        """c_own_ntt [B][nq_own][N], evk_own [beta][2][n_own][N], addend_own [B][2][nq_own][N] -> out [B][2][nq_own][N]"""
+        L = self.L
+        B = c_own_ntt.shape[0]
+        if out is None:
+            out = torch.empty((B, 2, max(self.nq_own, 1), self.ctx.N), dtype=torch.int64, device=self.device)
+        s = stream if stream is not None else torch.cuda.current_stream(self.device).cuda_stream
+        rc = L.lib().lsb_ks_shard_run(self.h, c_own_ntt.data_ptr(), evk_own.data_ptr(), addend_own.data_ptr() if addend_own is not None else None,
+                                      out.data_ptr(), B, s)
+        if rc != 0:
+            raise L.LsbError(L.lib().lsb_ks_shard_last_error().decode())
+        return out
+
+    def all_gather_bytes(self):
+        return int(self.L.lib().lsb_ks_shard_all_gather_bytes(self.h))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.lib().lsb_ks_shard_destroy(self.h)
+            self.h = None

@@ -95,3 +95,33 @@ def test_n65536_sharded_over_8_ranks():
     evk = _rand_evk(o, rng, level)
     assert np.array_equal(_run_emulated(ctx, params, level, 8, ct3, evk, True), o.relin(ct3, evk))
     ctx.close()
+
+
+@pytest.mark.parametrize("params,level,batch", [(R.CKKS_N13, None, 3), (R.CKKS_BTP_N13, 24, 2)], ids=["ckks8k-B3", "btp8k-L24-B2"])
+def test_cpp_nccl_driver_world1_matches_oracle(params, level, batch):
+    """The C++ host driver (lsb_ks_shard_create / lsb_ks_shard_run: NCCL loaded at run time, communicator, exchange
+    buffers, CUDA graph) on a one-rank world: the all-gathers degenerate to copies, every limb must equal the oracle's
+    relinearisation; the eager first call, the capturing second call and the graph replay give the same limbs."""
+    from lattisense_b200.dist import NcclShardedKeySwitch
+    o = R.Oracle(params)
+    ctx = L.Context(params.scheme, params.logN, params.q, params.p, params.t)
+    level = params.max_level if level is None else level
+    rng = np.random.default_rng(31)
+    cts = [_rand_ct(o, rng, level, 3) for _ in range(batch)]
+    evk = _rand_evk(o, rng, level)
+    sk = NcclShardedKeySwitch(ctx, level, 1, 0, max_batch=batch)
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        c_own = _dev(np.stack([ct[2] for ct in cts]))
+        add_own = _dev(np.stack([ct[:2] for ct in cts]))
+        evk_d = _dev(evk)
+        out = torch.empty((batch, 2, level + 1, ctx.N), dtype=torch.int64, device="cuda")
+        want = np.stack([o.relin(ct, evk) for ct in cts])
+        for it in range(3):  # eager, capture + launch, replay
+            out.zero_()
+            sk.run(c_own, evk_d, add_own, out=out, stream=s.cuda_stream)
+            s.synchronize()
+            assert np.array_equal(out.cpu().numpy().view(np.uint64), want), "iteration %d" % it
+    assert sk.all_gather_bytes() == batch * ((level + 1) + 2 * len(params.p)) * ctx.N * 8
+    sk.close()
+    ctx.close()

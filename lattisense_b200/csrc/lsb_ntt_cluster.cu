@@ -23,7 +23,7 @@
 #include "lsb_ntt_persist_core.h"
 
 #ifndef LSB_FIN_PREFETCH
-#define LSB_FIN_PREFETCH 1
+#define LSB_FIN_PREFETCH 0  // measured: +0.6 GB of DRAM reads per step (prefetched lines evicted before use), no time gain
 #endif
 #ifndef LSB_CL_RMAJOR
 #define LSB_CL_RMAJOR 0

@@ -395,6 +395,11 @@ def run_ours(args):
     prof = {k: ctx.profile_read(i) for i, k in enumerate(kinds)}
     ctx.profile(False)
     peak, peak_src = peaks()
+    try:
+        with open(os.path.join(ROOT, "profiles", "r02_traffic.json")) as f:
+            traffic = json.load(f)
+    except Exception:
+        traffic = {}
     tot_ms = sum(v[0] for v in prof.values())
     ntt_ms = prof["ntt_fwd"][0] + prof["ntt_inv"][0]
     ntt_bytes = prof["ntt_fwd"][2] + prof["ntt_inv"][2]
@@ -543,9 +548,11 @@ def run_ours(args):
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": "k_ntt_cluster<14,*,ArithF64> (forward incl. its fused finish epilogue + inverse, in-step average)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     # DRAM bytes per launch: ncu --set full measured 0.974 x the algorithmic 16*N bytes per limb transform
-                     # (profiles/r01_ntt14_cluster_ncu.txt: 1.075 GB read + 1.018 GB written for 8192 limbs of N=2^14)
-                     "traffic": 0.974 * ntt_bytes / max(ntt_k, 1),
+                     # DRAM bytes per NTT launch and the step-level traffic ratio come from an ncu capture of one step of this
+                     # build (tools/step_traffic.py -> profiles/r02_traffic.json), NOT from the timed run: labelled as such
+                     "traffic": traffic.get("ntt_dram_bytes_per_launch"), "traffic_source": traffic.get("source"),
+                     "step_traffic_ratio": traffic.get("step_traffic_ratio"), "step_dram_bytes": traffic.get("step_dram_bytes"),
+                     "step_fp64_pipe_busy_ms": traffic.get("fp64_pipe_busy_ms"),
                      "algorithmic_bytes_per_launch": ntt_bytes / max(ntt_k, 1),
                      # second roof: the FP64 pipe, 1.015 M DFMA-class ops per limb transform at the measured
                      # 57.8 lanes/clk/SM = 4.36 TB/s of algorithmic NTT traffic if the pipe never idled

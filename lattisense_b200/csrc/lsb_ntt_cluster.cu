@@ -649,7 +649,9 @@ template <int LOGN, class K>
 static void launch_cluster_k(K kernel, const NttClArgs& a, cudaStream_t s) {
     typedef ClusterCfg<LOGN> C;
     constexpr int smem = C::TILE * 8;
-    // (measured and dropped: prefetch.global.L1 of the next round's twiddles before each barrier, 2464 vs 2601 GB/s --
+    // (measured and dropped: padding the dynamic shared memory so that only 7 / 6 / 5 NTT CTAs fit an SM and the other
+    //  stream's HBM-bound kernels of the two-stream pipeline co-reside: 6.04 / 6.31 / 6.63 ms per cfg2 step against 5.70;
+    //  prefetch.global.L1 of the next round's twiddles before each barrier, 2464 vs 2601 GB/s --
     //  the kernel is short of issue slots, not of latency hiding; running every K-th FP64-eligible limb on the integer policy inside the same launch, to use
     //  both multiply pipes of an SM, was slower for every K -- 2.12 TB/s at K=4 against 2.60 TB/s; issue slots bind)
     LSB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

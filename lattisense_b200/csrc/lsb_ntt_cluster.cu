@@ -22,6 +22,16 @@
 #include "lsb_ntt_cluster_core.h"
 #include "lsb_ntt_persist_core.h"
 
+// N = 2^16: 8 CTAs per limb hold 64 KiB tiles (3 CTAs = 24 warps per SM; ncu: 31 % warps active, long-scoreboard bound,
+// profiles/r02_ks16_integer_ncu.txt); 16 CTAs per limb (non-portable cluster size) halve the tile: measured on the
+// level-24 key-switch (60/61-bit primes) 6.11 -> 5.57 ms at batch 16, 0.606 -> 0.491 ms for a single ciphertext (4 CTAs
+// per SM asked of ptxas; 3 / 5 / 6 were slower)
+#ifndef LSB_CL16
+#define LSB_CL16 16
+#endif
+#ifndef LSB_CL16_MINB
+#define LSB_CL16_MINB 4
+#endif
 #ifndef LSB_FIN_PREFETCH
 #define LSB_FIN_PREFETCH 0  // measured: +0.6 GB of DRAM reads per step (prefetched lines evicted before use), no time gain
 #endif
@@ -53,7 +63,7 @@ namespace lsb {
 template <int LOGN>
 struct ClusterCfg {
     static constexpr int N = 1 << LOGN;
-    static constexpr int CL = LOGN <= 12 ? 1 : LOGN == 13 ? 2 : LOGN == 14 ? LSB_CL14 : 8;  // CTAs per limb
+    static constexpr int CL = LOGN <= 12 ? 1 : LOGN == 13 ? 2 : LOGN == 14 ? LSB_CL14 : LOGN == 16 ? LSB_CL16 : 8;  // CTAs per limb
     static constexpr int BS = N / 16;                                                 // block = sub-transform size
     static constexpr int LS = LOGN - 4;
     static constexpr int NB = 16 / CL;      // blocks per CTA
@@ -61,7 +71,7 @@ struct ClusterCfg {
     static constexpr int NT = LOGN == 14 ? LSB_CL14_NT : LSB_CL_NT;
     // resident CTAs per SM asked of ptxas; N = 2^16 tiles are 64 KiB, so only 3 fit anyway and asking for 3 leaves the
     // compiler 85 registers (inverse: 1365 -> 1538 GB/s on the mixed chain, 1004 -> 1098 GB/s on 61-bit primes)
-    static constexpr int MINB = LOGN == 14 ? LSB_CL14_MINB : LOGN == 16 ? 3 : LSB_CL_MINB;
+    static constexpr int MINB = LOGN == 14 ? LSB_CL14_MINB : LOGN == 16 ? LSB_CL16_MINB : LSB_CL_MINB;
     static constexpr int G0 = BS / CL;      // cross-round groups per CTA
 };
 
@@ -655,6 +665,7 @@ static void launch_cluster_k(K kernel, const NttClArgs& a, cudaStream_t s) {
     //  the kernel is short of issue slots, not of latency hiding; running every K-th FP64-eligible limb on the integer policy inside the same launch, to use
     //  both multiply pipes of an SM, was slower for every K -- 2.12 TB/s at K=4 against 2.60 TB/s; issue slots bind)
     LSB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    if (C::CL > 8) LSB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(a.total_rows * C::CL), 1, 1);
     cfg.blockDim = dim3(C::NT, 1, 1);

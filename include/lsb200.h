@@ -87,6 +87,10 @@ int lsb_drop_level(lsb_context_t ctx, int level, int npoly, const uint64_t* d_in
  * (gal = 5^step mod 2N for columns, 2N-1 for rows / conjugate; frontend/custom_task.py:139-145) + key-switch. */
 int lsb_rotate(lsb_context_t ctx, int level, const uint64_t* d_ct, const uint64_t* d_glk, int key_level,
                uint64_t galois_element, uint64_t* d_out, int batch, void* stream);
+/* n_rot rotations of the same ciphertexts with ONE shared decomposition (hoisted rotations, the baby steps of a BSGS linear
+ * transform: frontend/custom_task.py:1427-1457): d_out[r] = lsb_rotate(d_ct, d_glk[r], galois_elements[r]) bit for bit. */
+int lsb_rotate_hoisted(lsb_context_t ctx, int level, const uint64_t* d_ct, int n_rot, const uint64_t* const* d_glk, int key_level,
+                       const uint64_t* galois_elements, uint64_t* const* d_out, int batch, void* stream);
 /* bind_gpu_add / sub / neg (mega_ag_executors_gpu.cu:71-175). */
 int lsb_add(lsb_context_t ctx, int level, int npoly, const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_out,
             int batch, void* stream);

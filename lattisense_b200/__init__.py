@@ -77,6 +77,7 @@ def lib():
     L.lsb_ks_shard_begin_p2p.argtypes = [vp, ci, ci, ci, vp, vp, vp]
     L.lsb_ks_shard_inner_p2p.argtypes = [vp, ci, ci, ci, vp, vp, vp, vp, vp, vp]
     L.lsb_ks_shard_end.argtypes = [vp, ci, ci, ci, vp, vp, vp, vp, ci, vp]
+    L.lsb_rotate_hoisted.argtypes = [vp, ci, vp, ci, C.POINTER(C.c_void_p), ci, u64p, C.POINTER(C.c_void_p), ci, vp]
     L.lsb_mac.argtypes = [vp, ci, ci, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), ci, vp, vp, ci, vp]
     L.lsb_bootstrap_create.restype = C.c_void_p
     L.lsb_bootstrap_create.argtypes = [vp, i32p, C.POINTER(C.c_double)]
@@ -365,6 +366,22 @@ class Context:
 
     def mul_plain_ringt(self, ct, pt):
         return self._plain("lsb_mul_plain_ringt", ct, pt)
+
+    def rotate_hoisted(self, ct, glks, gals):
+        """[rotate(ct, glk, gal) for glk, gal in zip(glks, gals)] with one shared decomposition (lsb_rotate_hoisted)"""
+        ct = np.ascontiguousarray(ct, dtype=np.uint64)
+        batched = ct.ndim == 4
+        B = ct.shape[0] if batched else 1
+        level = ct.shape[-2] - 1
+        key_level = glks[0].shape[2] - self.k - 1
+        d = self.upload(ct)
+        dk = [self.upload(k) for k in glks]
+        outs = [DevBuf(self, ct.size) for _ in glks]
+        pk = (C.c_void_p * len(dk))(*[x.ptr for x in dk])
+        po = (C.c_void_p * len(outs))(*[x.ptr for x in outs])
+        ga = np.array(gals, dtype=np.uint64)
+        _check(lib().lsb_rotate_hoisted(self.h, level, d.ptr, len(dk), pk, key_level, ga.ctypes.data_as(u64p), po, B, self.stream))
+        return [self.download(o, ct.shape) for o in outs]
 
     def mac(self, cts, pts, ringt=False, acc=None):
         """sum_i cts[i] x pts[i] (+ acc): bind_gpu_cmp_sum / bind_gpu_cmpac_sum.  cts[i] [2][l][N] (or [B][2][l][N])."""

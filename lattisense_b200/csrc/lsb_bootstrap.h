@@ -300,6 +300,7 @@ inline void chebyshev_split(const std::vector<long double>& c, int m, std::vecto
 //   typedef Ct, Pt (movable handles);  int level(const Ct&)
 //   Pt make_plain(int level, const std::vector<u64>& coeff_limbs)   coefficient-domain residues [level+1][N] -> NTT domain
 //   Ct rotate(const Ct&, int step)    Ct conjugate(const Ct&)        Galois keys 5^step mod 2N / 2N-1
+//   vector<Ct> rotate_many(const Ct&, steps)                          the same rotations, free to share the decomposition
 //   Ct switch_key(const Ct&, int which)                               0: swk_dts, 1: swk_std (no automorphism)
 //   Ct mod_raise(const Ct& level0, int top)
 //   Ct add(a, b)  Ct sub(a, b)  Ct mul_relin(a, b)  Ct rescale(a)  Ct drop_to(a, level)
@@ -441,13 +442,17 @@ private:
         if (ops.level(in.ct) != e.level) throw std::runtime_error("lsb bootstrap: linear transform at the wrong level");
         std::map<int, Ct> baby;
         std::map<int, std::vector<std::pair<int, const Pt*>>> groups;
+        std::vector<int> steps;
         for (size_t i = 0; i < e.rot.size(); i++) {
             const int k = e.rot[i], b = k % e.n1, g = k - b;
             groups[g].push_back({b, &e.pt[i]});
-            if (b && !baby.count(b)) {
-                baby.emplace(b, ops.rotate(in.ct, b));
-                st.rotations++;
-            }
+            if (b && std::find(steps.begin(), steps.end(), b) == steps.end()) steps.push_back(b);
+        }
+        if (!steps.empty()) {
+            // all baby steps rotate the same ciphertext: one shared decomposition (hoisting), limbs as rotate()'s
+            std::vector<Ct> rot = ops.rotate_many(in.ct, steps);
+            for (size_t i = 0; i < steps.size(); i++) baby.emplace(steps[i], std::move(rot[i]));
+            st.rotations += (int)steps.size();
         }
         std::vector<Ct> parts;
         for (auto& gi : groups) {

@@ -95,6 +95,33 @@ struct DevOps {
         return o;
     }
     Ct rotate(const Ct& a, int step) { return rotate_gal(a, gal_of(step)); }
+    const u64* key_of(u64 gal) const {
+        for (size_t i = 0; i < keys.gal.size(); i++)
+            if (keys.gal[i] == gal) return keys.glk[i];
+        throw std::runtime_error("lsb bootstrap: the task carries no Galois key for element " + std::to_string(gal));
+    }
+    std::vector<Ct> rotate_many(const Ct& a, const std::vector<int>& steps) {
+        static const bool hoist = [] {  // LSB_BTP_HOIST=0: one full key-switch per rotation (A/B; limbs are identical)
+            const char* e = getenv("LSB_BTP_HOIST");
+            return !(e && atoi(e) == 0);
+        }();
+        std::vector<Ct> out;
+        if (!hoist || steps.size() < 2) {
+            for (int st : steps) out.push_back(rotate(a, st));
+            return out;
+        }
+        std::vector<const u64*> ks;
+        std::vector<u64> gals;
+        std::vector<BatchPtr> outs;
+        for (int st : steps) {
+            gals.push_back(gal_of(st));
+            ks.push_back(key_of(gals.back()));
+            out.push_back(make(a.level));
+            outs.push_back(bp(out.back()));
+        }
+        op_rotate_hoisted(e, a.level, bp(a), (int)steps.size(), ks.data(), keys.key_level, gals.data(), outs.data(), batch);
+        return out;
+    }
     Ct conjugate(const Ct& a) { return rotate_gal(a, 2 * (u64)N - 1); }
     Ct switch_key(const Ct& a, int which) {
         Ct o = make(a.level);

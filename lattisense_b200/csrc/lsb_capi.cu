@@ -323,6 +323,16 @@ int lsb_ks_shard_end(lsb_context_t h, int level, int world, int rank, const uint
 }
 
 
+int lsb_rotate_hoisted(lsb_context_t h, int level, const uint64_t* d_ct, int n_rot, const uint64_t* const* d_glk, int key_level,
+                       const uint64_t* gals, uint64_t* const* d_out, int batch, void* stream) {
+    return run_op(h, stream, [&](OpEnv& e) {
+        LSB_CHECK(n_rot >= 1 && d_glk && gals && d_out, "lsb: rotate_hoisted: bad arguments");
+        const size_t w = e.c.ct_words(level, 2);
+        std::vector<BatchPtr> outs(n_rot);
+        for (int r = 0; r < n_rot; r++) outs[r] = dense(d_out[r], w);
+        op_rotate_hoisted(e, level, dense(d_ct, w), n_rot, d_glk, key_level, gals, outs.data(), batch);
+    });
+}
 int lsb_mac(lsb_context_t h, int level, int nterms, const uint64_t* const* d_cts, const uint64_t* const* d_pts, int ringt,
             const uint64_t* d_acc, uint64_t* d_out, int batch, void* stream) {
     return run_op(h, stream, [&](OpEnv& e) {

@@ -70,36 +70,41 @@ static int ks_scratch_limbs(const Context& c, int level) {
     return c.beta(level) * lk + 2 * lk + 2 * l;
 }
 
+// The key-switch in two halves, so that several rotations of ONE ciphertext share the first ("hoisting": the CKKS rotation
+// key-switches the un-permuted c1 and permutes afterwards, so the decomposition does not depend on the Galois element):
+//   ks_decompose: ModUp of the beta digits + NTT of the extended limbs            -> ext [beta][l+k]
+//   ks_apply:     inner product with the key, INTT of the P limbs, ModDown, NTT + finish
 // res[p*res_ps + i] = (acc_p[i] - md_p[i]) * P^-1 (+ addend[p*l + i] if addmask bit p), NTT domain
-static void ks_core(OpEnv& e, int level, BatchPtr c_coeff, int coeff_slot0, BatchPtr c_ntt, int ntt_slot0,
-                    const u64* evk, int key_level, BatchPtr addend, int addmask, BatchPtr res, int res_ps,
-                    u64* scratch, size_t item_words, int nb) {
+static void ks_decompose(OpEnv& e, int level, BatchPtr c_coeff, int coeff_slot0, BatchPtr ext, int nb) {
+    Context& c = e.c;
+    const DeviceTables& dt = c.dt;
+    const int l = level + 1, k = c.np, lk = l + k, beta = c.beta(level), alpha = k;
+    {
+        const BexJob* jobs = c.modup_jobs(level, coeff_slot0);
+        launch_basis_extend(dt, jobs, beta, c_coeff, ext, ext, nb, e.s, c.bex_meta(jobs));
+    }
+    RowMap m;
+    m.n = 0;
+    for (int d = 0; d < beta; d++)
+        for (int t = 0; t < lk; t++) {
+            if (t < l && t >= d * alpha && t < (d + 1) * alpha) continue;
+            LSB_CHECK(m.n < kMaxRows, "lsb: too many extended limbs");
+            m.in_slot[m.n] = m.out_slot[m.n] = (uint8_t)(d * lk + t);
+            m.mod[m.n] = (uint8_t)(t < l ? t : c.idxP(t - l));
+            m.n++;
+        }
+    launch_ntt(dt, ext, ext, m, nb, false, e.s);
+}
+// scratch: [acc 2(l+k) | md 2l] limbs per item
+static void ks_apply(OpEnv& e, int level, BatchPtr ext, BatchPtr c_ntt, int ntt_slot0, const u64* evk, int key_level, BatchPtr addend,
+                     int addmask, BatchPtr res, int res_ps, u64* scratch, size_t item_words, int nb) {
     Context& c = e.c;
     const DeviceTables& dt = c.dt;
     const int l = level + 1, k = c.np, lk = l + k, beta = c.beta(level), alpha = k;
     const size_t N = c.N;
     LSB_CHECK(key_level >= level, "lsb: evaluation key level below ciphertext level");
-    BatchPtr ext = bp_strided(scratch, item_words);
-    BatchPtr acc = bp_strided(scratch + (size_t)beta * lk * N, item_words);
-    BatchPtr md = bp_strided(scratch + (size_t)(beta * lk + 2 * lk) * N, item_words);
-
-    {
-        const BexJob* jobs = c.modup_jobs(level, coeff_slot0);
-        launch_basis_extend(dt, jobs, beta, c_coeff, ext, ext, nb, e.s, c.bex_meta(jobs));
-    }
-    {
-        RowMap m;
-        m.n = 0;
-        for (int d = 0; d < beta; d++)
-            for (int t = 0; t < lk; t++) {
-                if (t < l && t >= d * alpha && t < (d + 1) * alpha) continue;
-                LSB_CHECK(m.n < kMaxRows, "lsb: too many extended limbs");
-                m.in_slot[m.n] = m.out_slot[m.n] = (uint8_t)(d * lk + t);
-                m.mod[m.n] = (uint8_t)(t < l ? t : c.idxP(t - l));
-                m.n++;
-            }
-        launch_ntt(dt, ext, ext, m, nb, false, e.s);
-    }
+    BatchPtr acc = bp_strided(scratch, item_words);
+    BatchPtr md = bp_strided(scratch + (size_t)(2 * lk) * N, item_words);
     KsInnerArgs ia;
     ia.ext = ext;
     ia.cntt = c_ntt;
@@ -146,6 +151,14 @@ static void ks_core(OpEnv& e, int level, BatchPtr c_coeff, int coeff_slot0, Batc
         NttFinish fin{fm, c.finish_host(fm), acc, addend, res, addmask != 0};
         launch_ntt_finish(dt, md, fin, nb, e.s);
     }
+}
+static void ks_core(OpEnv& e, int level, BatchPtr c_coeff, int coeff_slot0, BatchPtr c_ntt, int ntt_slot0,
+                    const u64* evk, int key_level, BatchPtr addend, int addmask, BatchPtr res, int res_ps,
+                    u64* scratch, size_t item_words, int nb) {
+    const int l = level + 1, lk = l + e.c.np, beta = e.c.beta(level);
+    BatchPtr ext = bp_strided(scratch, item_words);
+    ks_decompose(e, level, c_coeff, coeff_slot0, ext, nb);
+    ks_apply(e, level, ext, c_ntt, ntt_slot0, evk, key_level, addend, addmask, res, res_ps, scratch + (size_t)beta * lk * e.c.N, item_words, nb);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -533,6 +546,35 @@ void op_scalar(OpEnv& e, int level, int npoly, BatchPtr ct, const u64* residues,
     Tw consts[64];
     for (int i = 0; i < l; i++) consts[i] = host::make_tw(residues[i] % e.c.moduli[i], e.c.moduli[i]);
     launch_scalar(e.c.dt, ct, out, npoly, l, consts, add, batch, e.s);
+}
+
+// n_rot rotations of the SAME ciphertexts with one shared decomposition (CKKS): out_r = rotate(ct, gal_r).  Every limb
+// equals op_rotate's (the same kernels on the same data; only the ModUp + forward NTT of the digits is done once).
+// Reference: the hoisted baby-step rotations the frontend sketches for BSGS (custom_task.py:1427-1457).
+void op_rotate_hoisted(OpEnv& e, int level, BatchPtr ct, int n_rot, const u64* const* glk, int key_level, const u64* gal, const BatchPtr* out,
+                       int batch) {
+    LSB_CUDA(cudaSetDevice(e.c.device));
+    Context& c = e.c;
+    LSB_CHECK(c.scheme == SCHEME_CKKS, "lsb: hoisted rotations are a CKKS (NTT-domain) operation");
+    const int l = level + 1, lk = l + c.np, beta = c.beta(level);
+    const size_t N = c.N;
+    // [c1x l | ext beta*lk | tmp 2l | acc 2lk | md 2l]
+    const size_t item = (size_t)(l + beta * lk + 2 * l + 2 * lk + 2 * l) * N;
+    const int chunk = pick_chunk(e, item, batch, beta * lk - l);
+    u64* scratch = e.ws.reserve(item * chunk, e.s);
+    for (int b0 = 0; b0 < batch; b0 += chunk) {
+        const int nb = std::min(chunk, batch - b0);
+        BatchPtr c1x = bp_strided(scratch, item);
+        BatchPtr ext = bp_strided(scratch + (size_t)l * N, item);
+        BatchPtr tmp = bp_strided(scratch + (size_t)(l + beta * lk) * N, item);
+        u64* rest = scratch + (size_t)(l + beta * lk + 2 * l) * N;
+        launch_ntt(c.dt, adv(ct, b0), c1x, rowmap_seq(l, l, 0, 0, l), nb, true, e.s);
+        ks_decompose(e, level, c1x, 0, ext, nb);
+        for (int r = 0; r < n_rot; r++) {
+            ks_apply(e, level, ext, adv(ct, b0), l, glk[r], key_level, adv(ct, b0), 1, tmp, l, rest, item, nb);
+            launch_permute_ntt(c.dt, tmp, adv(out[r], b0), rowmap_seq(2 * l, 0, 0, 0, l), c.permute_index(gal[r]), nb, e.s);
+        }
+    }
 }
 
 // ---------------------------------------------------------------------------------------------

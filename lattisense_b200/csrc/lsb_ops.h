@@ -32,6 +32,9 @@ void op_switch_key(OpEnv& e, int level, BatchPtr ct, const u64* swk, int key_lev
 void op_scalar(OpEnv& e, int level, int npoly, BatchPtr ct, const u64* residues, bool add, BatchPtr out, int batch);
 // bind_gpu_rotate_col / bind_gpu_rotate_row (:264-292): automorphism gal + key-switch under glk[gal]
 void op_rotate(OpEnv& e, int level, BatchPtr ct, const u64* glk, int key_level, u64 gal, BatchPtr out, int batch);
+// several rotations of the same ciphertexts sharing one decomposition (hoisting); limbs equal op_rotate's
+void op_rotate_hoisted(OpEnv& e, int level, BatchPtr ct, int n_rot, const u64* const* glk, int key_level, const u64* gal, const BatchPtr* out,
+                       int batch);
 // bind_gpu_add / sub / neg (:71-175), ct (op) ct with npoly polynomials
 void op_add(OpEnv& e, int level, int npoly, BatchPtr a, BatchPtr b, BatchPtr out, int batch);
 void op_sub(OpEnv& e, int level, int npoly, BatchPtr a, BatchPtr b, BatchPtr out, int batch);

@@ -61,6 +61,11 @@ struct OracleOps {
     }
     Ct rotate(const Ct& a, int step) const { return rotate_gal(a, gal_of(step)); }
     Ct conjugate(const Ct& a) const { return rotate_gal(a, 2 * N - 1); }
+    std::vector<Ct> rotate_many(const Ct& a, const std::vector<int>& steps) const {
+        std::vector<Ct> out;
+        for (int st : steps) out.push_back(rotate(a, st));
+        return out;
+    }
     Ct switch_key(const Ct& a, int which) const {
         const int l = a.level + 1;
         Ct o = make(a.level);

@@ -370,3 +370,23 @@ def test_mac_parity(params, m, with_acc, ringt):
     got = g.mac(cts, pts, ringt=ringt, acc=acc)
     assert np.array_equal(got, want)
     g.close()
+
+
+@pytest.mark.parametrize("params,level", [(R.CKKS_N13, None), (R.CKKS_BTP_N13, 20), (R.CKKS_WIDE_N13, 4)], ids=["ckks8k", "btp8k-L20", "wide8k-L4"])
+def test_hoisted_rotations_equal_plain_rotations(params, level):
+    """lsb_rotate_hoisted (one decomposition shared by several rotations of the same ciphertext) gives, for every rotation,
+    the limbs of the oracle's rotate -- the same as lsb_rotate."""
+    o = R.Oracle(params)
+    g = _ctx(params)
+    level = params.max_level if level is None else level
+    rng = np.random.default_rng(9)
+    s = o.gen_secret(4)
+    ct = np.stack([np.stack([rng.integers(0, q, size=(2, o.N), dtype=np.uint64) for q in params.q[:level + 1]], axis=1) for _ in range(2)])
+    steps = [1, 5, 100, o.N // 2 - 3]
+    gals = [R.galois_for_col_step(o.N, st) for st in steps] + [R.galois_for_row(o.N)]
+    glks = [o.gen_glk(s, 50 + i, level, gal) for i, gal in enumerate(gals)]
+    got = g.rotate_hoisted(ct, glks, gals)
+    for r, (gal, glk) in enumerate(zip(gals, glks)):
+        for b in range(2):
+            assert np.array_equal(got[r][b], o.rotate(ct[b], glk, gal)), (r, b)
+    g.close()

@@ -335,19 +335,37 @@ __global__ void __launch_bounds__(kElemThreads) k_bex_f64(const __grid_constant_
     u64* pd = g.dst.at(b);
     const size_t N = g.N;
     double ya[NS], yb[NS];
-    double vfa = 0.0, vfb = 0.0;
+    // The overflow count is floor of Lattigo's float64 sum  v = (..(y_0/s_0) + y_1/s_1 ..)  -- divisions, in limb order.
+    // A double division costs ~20 FP64-pipe instructions and this kernel is FP64-pipe bound, so the sum is first formed
+    // with multiplications by 1/s_i: the two sums differ by less than NS * 2^-51, hence have the same floor unless the
+    // fast one lies within 2^-40 of an integer; only then (probability ~2^-39 per coefficient) is the exact sequence run.
+    double vma = 0.0, vmb = 0.0;
 #pragma unroll
     for (int i = 0; i < NS; i++) {
         const W2 x = ld2(ps + (size_t)job.src_slot[i] * N, j2);
         const ModConst& ms = g.mods[job.src_mod[i]];
         const TwD qi = job.qhat_inv_d[i];
-        const double sf = job.s_f64[i];
         ya[i] = f64_canon_d(f64_mulmod(f64_from_u64(x.a), qi, ms.qd), ms.qd, ms.qinvd);
         yb[i] = f64_canon_d(f64_mulmod(f64_from_u64(x.b), qi, ms.qd), ms.qd, ms.qinvd);
-        vfa += ya[i] / sf;  // same float64 overflow estimate, same summation order as the generic path
-        vfb += yb[i] / sf;
+        vma = d_fma(ya[i], job.rs_f64[i], vma);
+        vmb = d_fma(yb[i], job.rs_f64[i], vmb);
     }
-    const int va = (int)(u64)vfa, vb = (int)(u64)vfb;
+    int va = (int)vma, vb = (int)vmb;
+    {
+        const double eps = 9.094947017729282e-13;  // 2^-40
+        const double fa = vma - (double)va, fb = vmb - (double)vb;
+        if (fa < eps || fa > 1.0 - eps || fb < eps || fb > 1.0 - eps) {
+            double vfa = 0.0, vfb = 0.0;
+#pragma unroll
+            for (int i = 0; i < NS; i++) {
+                const double sf = job.s_f64[i];
+                vfa += ya[i] / sf;  // same float64 overflow estimate, same summation order as the generic path
+                vfb += yb[i] / sf;
+            }
+            va = (int)(u64)vfa;
+            vb = (int)(u64)vfb;
+        }
+    }
     for (int t = 0; t < nt; t++) {
         const BexTargetC<NS>& c = sh[t];
         double aa = 0.0, ab = 0.0;

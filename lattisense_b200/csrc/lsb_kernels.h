@@ -56,6 +56,7 @@ struct BexJob {
     uint8_t dst_slot[kBexMaxDst], dst_mod[kBexMaxDst], other_slot[kBexMaxDst];
     Tw qhat_inv[kBexMaxSrc];
     double s_f64[kBexMaxSrc];
+    double rs_f64[kBexMaxSrc];  // 1 / s_f64 (fast overflow estimate; the exact division is the fallback near integers)
     u64 qhat_mod[kBexMaxDst][kBexMaxSrc];
     u64 vS[kBexMaxDst][kBexMaxSrc + 1];
     Tw mulc[kBexMaxDst];

@@ -94,6 +94,7 @@ inline BexJob make_bex_tables(const std::vector<u64>& moduli, const std::vector<
         const u64 si = moduli[src[i]];
         j.src_mod[i] = (uint8_t)src[i];
         j.s_f64[i] = (double)si;
+        j.rs_f64[i] = 1.0 / (double)si;
         u64 prod = 1;
         for (int k = 0; k < j.ns; k++)
             if (k != i) prod = mulmod(prod, moduli[src[k]] % si, si);

@@ -390,3 +390,23 @@ def test_hoisted_rotations_equal_plain_rotations(params, level):
         for b in range(2):
             assert np.array_equal(got[r][b], o.rotate(ct[b], glk, gal)), (r, b)
     g.close()
+
+
+@pytest.mark.parametrize("params", [R.CKKS_N13, R.CKKS_N14, R.CKKS_WIDE_N13], ids=lambda p: p.name)
+def test_keyswitch_overflow_estimate_near_integers(params):
+    """The FP64 CRT kernel forms Lattigo's float64 overflow count with multiplications and falls back to the exact
+    division sequence when the sum lies within 2^-40 of an integer.  Digits whose CRT value is 0, +-1, +-2 (sum = k + tiny or
+    k - tiny) sit exactly there: the relinearisation of such a c2 must still equal the oracle's limb for limb."""
+    o = R.Oracle(params)
+    g = _ctx(params)
+    level = params.max_level
+    l = level + 1
+    rng = np.random.default_rng(77)
+    small = rng.integers(-2, 3, size=o.N)  # coefficient-domain c2 with values in {-2..2}: every digit's CRT value is tiny or Q_d - tiny
+    small[:8] = [0, 1, -1, 2, -2, 0, 1, -1]
+    c2c = np.stack([(small % q).astype(np.uint64) for q in params.q[:l]])
+    ct3 = np.stack([np.stack([rng.integers(0, q, size=o.N, dtype=np.uint64) for q in params.q[:l]]) for _ in range(2)] + [o.ntt_limbs(c2c)])
+    evk = np.stack([np.stack([np.stack([rng.integers(0, m, size=o.N, dtype=np.uint64) for m in params.q[:l] + params.p]) for _ in range(2)])
+                    for _ in range(params.beta(level))])
+    assert np.array_equal(g.relin(ct3, evk), o.relin(ct3, evk))
+    g.close()

@@ -307,6 +307,7 @@ inline void chebyshev_split(const std::vector<long double>& c, int m, std::vecto
 //   Ct mul_scalar(a, residues)   both polynomials times an integer constant given modulo q_0..q_level
 //   Ct add_scalar(a, residues)   constant added to every NTT slot of c0 (a constant polynomial)
 //   Ct mul_plain(a, pt)          Ct sum_products(cts, pts) = sum_i ct_i * pt_i      Ct sum(cts)
+//   Ct concat(a, b): the items of a followed by the items of b as one batch;   pair<Ct, Ct> split(c): its inverse
 template <class Ops>
 class Bootstrapper {
 public:
@@ -389,10 +390,12 @@ public:
         for (int i = 0; i < P.cts_depth; i++) v = linear(ops, v, cts_plain[i]);
         Ct vc = ops.conjugate(v.ct);
         st.key_switches++;
-        Sc t_re{ops.add(v.ct, vc), v.scale};
-        Sc t_im{ops.mul_plain(ops.sub(v.ct, vc), mono_neg_i), v.scale};
-        Sc y_re = eval_mod(ops, t_re), y_im = eval_mod(ops, t_im);
-        Sc z{ops.add(y_re.ct, ops.mul_plain(y_im.ct, mono_i)), y_re.scale};
+        // real and imaginary halves go through EvalMod as ONE stacked batch (the two evaluations are the same op sequence
+        // on independent ciphertexts): half the launches, twice the work per launch
+        Sc t{ops.concat(ops.add(v.ct, vc), ops.mul_plain(ops.sub(v.ct, vc), mono_neg_i)), v.scale};
+        Sc y = eval_mod(ops, t);
+        std::pair<Ct, Ct> halves = ops.split(y.ct);
+        Sc z{ops.add(halves.first, ops.mul_plain(halves.second, mono_i)), y.scale};
         for (int i = 0; i < P.stc_depth; i++) z = linear(ops, z, stc_plain[i]);
         return std::move(z.ct);
     }

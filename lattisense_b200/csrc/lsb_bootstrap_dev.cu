@@ -17,17 +17,19 @@ struct DevOps {
     struct Ct {
         u64* p = nullptr;
         int level = -1;
+        int nb = 0;  // batch items held (EvalMod runs on the real and imaginary halves stacked into one batch)
         cudaStream_t s = nullptr;
         Ct() = default;
-        Ct(u64* p_, int level_, cudaStream_t s_) : p(p_), level(level_), s(s_) {}
+        Ct(u64* p_, int level_, int nb_, cudaStream_t s_) : p(p_), level(level_), nb(nb_), s(s_) {}
         Ct(const Ct&) = delete;
         Ct& operator=(const Ct&) = delete;
-        Ct(Ct&& o) noexcept : p(o.p), level(o.level), s(o.s) { o.p = nullptr; }
+        Ct(Ct&& o) noexcept : p(o.p), level(o.level), nb(o.nb), s(o.s) { o.p = nullptr; }
         Ct& operator=(Ct&& o) noexcept {
             if (this != &o) {
                 release();
                 p = o.p;
                 level = o.level;
+                nb = o.nb;
                 s = o.s;
                 o.p = nullptr;
             }
@@ -55,10 +57,25 @@ struct DevOps {
 
     int level(const Ct& a) const { return a.level; }
     size_t words(int level) const { return (size_t)2 * (level + 1) * N; }
-    Ct make(int level) {
+    Ct make(int level, int nb) {
         u64* p = nullptr;
-        LSB_CUDA(cudaMallocAsync((void**)&p, words(level) * batch * sizeof(u64), e.s));
-        return Ct(p, level, e.s);
+        LSB_CUDA(cudaMallocAsync((void**)&p, words(level) * nb * sizeof(u64), e.s));
+        return Ct(p, level, nb, e.s);
+    }
+    Ct concat(const Ct& a, const Ct& b) {
+        LSB_CHECK(a.level == b.level, "lsb bootstrap: concat of different levels");
+        Ct o = make(a.level, a.nb + b.nb);
+        const size_t wa = words(a.level) * a.nb, wb = words(a.level) * b.nb;
+        LSB_CUDA(cudaMemcpyAsync(o.p, a.p, wa * sizeof(u64), cudaMemcpyDeviceToDevice, e.s));
+        LSB_CUDA(cudaMemcpyAsync(o.p + wa, b.p, wb * sizeof(u64), cudaMemcpyDeviceToDevice, e.s));
+        return o;
+    }
+    std::pair<Ct, Ct> split(const Ct& c) {
+        Ct a = make(c.level, c.nb / 2), b = make(c.level, c.nb - c.nb / 2);
+        const size_t wa = words(c.level) * a.nb, wb = words(c.level) * b.nb;
+        LSB_CUDA(cudaMemcpyAsync(a.p, c.p, wa * sizeof(u64), cudaMemcpyDeviceToDevice, e.s));
+        LSB_CUDA(cudaMemcpyAsync(b.p, c.p + wa, wb * sizeof(u64), cudaMemcpyDeviceToDevice, e.s));
+        return {std::move(a), std::move(b)};
     }
     BatchPtr bp(const Ct& a) const { return bp_strided(a.p, words(a.level)); }
 
@@ -90,8 +107,8 @@ struct DevOps {
         for (size_t i = 0; i < keys.gal.size(); i++)
             if (keys.gal[i] == gal) key = keys.glk[i];
         if (!key) throw std::runtime_error("lsb bootstrap: the task carries no Galois key for element " + std::to_string(gal));
-        Ct o = make(a.level);
-        op_rotate(e, a.level, bp(a), key, keys.key_level, gal, bp(o), batch);
+        Ct o = make(a.level, a.nb);
+        op_rotate(e, a.level, bp(a), key, keys.key_level, gal, bp(o), a.nb);
         return o;
     }
     Ct rotate(const Ct& a, int step) { return rotate_gal(a, gal_of(step)); }
@@ -116,59 +133,59 @@ struct DevOps {
         for (int st : steps) {
             gals.push_back(gal_of(st));
             ks.push_back(key_of(gals.back()));
-            out.push_back(make(a.level));
+            out.push_back(make(a.level, a.nb));
             outs.push_back(bp(out.back()));
         }
-        op_rotate_hoisted(e, a.level, bp(a), (int)steps.size(), ks.data(), keys.key_level, gals.data(), outs.data(), batch);
+        op_rotate_hoisted(e, a.level, bp(a), (int)steps.size(), ks.data(), keys.key_level, gals.data(), outs.data(), a.nb);
         return out;
     }
     Ct conjugate(const Ct& a) { return rotate_gal(a, 2 * (u64)N - 1); }
     Ct switch_key(const Ct& a, int which) {
-        Ct o = make(a.level);
+        Ct o = make(a.level, a.nb);
         op_switch_key(e, a.level, bp(a), which == 0 ? keys.swk_dts : keys.swk_std, which == 0 ? keys.swk_dts_level : keys.key_level, bp(o),
-                      batch);
+                      a.nb);
         return o;
     }
     Ct mod_raise(const Ct& a, int top) {
         LSB_CHECK(a.level == 0, "lsb bootstrap: mod_raise expects a level-0 ciphertext");
-        Ct o = make(top);
-        op_mod_raise(e, top, 2, bp(a), bp(o), batch);
+        Ct o = make(top, a.nb);
+        op_mod_raise(e, top, 2, bp(a), bp(o), a.nb);
         return o;
     }
     Ct add(const Ct& a, const Ct& b) {
-        Ct o = make(a.level);
-        op_add(e, a.level, 2, bp(a), bp(b), bp(o), batch);
+        Ct o = make(a.level, a.nb);
+        op_add(e, a.level, 2, bp(a), bp(b), bp(o), a.nb);
         return o;
     }
     Ct sub(const Ct& a, const Ct& b) {
-        Ct o = make(a.level);
-        op_sub(e, a.level, 2, bp(a), bp(b), bp(o), batch);
+        Ct o = make(a.level, a.nb);
+        op_sub(e, a.level, 2, bp(a), bp(b), bp(o), a.nb);
         return o;
     }
     Ct mul_relin(const Ct& a, const Ct& b) {
         LSB_CHECK(a.level == b.level, "lsb bootstrap: ct x ct operands at different levels");
-        Ct o = make(a.level);
-        op_mult_relin(e, a.level, bp(a), bp(b), keys.rlk, keys.key_level, bp(o), batch);
+        Ct o = make(a.level, a.nb);
+        op_mult_relin(e, a.level, bp(a), bp(b), keys.rlk, keys.key_level, bp(o), a.nb);
         return o;
     }
     Ct rescale(const Ct& a) {
-        Ct o = make(a.level - 1);
-        op_rescale(e, a.level, 2, bp(a), bp(o), batch);
+        Ct o = make(a.level - 1, a.nb);
+        op_rescale(e, a.level, 2, bp(a), bp(o), a.nb);
         return o;
     }
     Ct drop_to(const Ct& a, int level) {
-        Ct o = make(level);
-        op_drop_to(e, a.level, level, 2, bp(a), bp(o), batch);
+        Ct o = make(level, a.nb);
+        op_drop_to(e, a.level, level, 2, bp(a), bp(o), a.nb);
         return o;
     }
     Ct mul_scalar(const Ct& a, const std::vector<u64>& k) {
-        Ct o = make(a.level);
-        op_scalar(e, a.level, 2, bp(a), k.data(), false, bp(o), batch);
+        Ct o = make(a.level, a.nb);
+        op_scalar(e, a.level, 2, bp(a), k.data(), false, bp(o), a.nb);
         return o;
     }
     Ct add_scalar(const Ct& a, const std::vector<u64>& k) {
-        Ct o = make(a.level);
-        op_scalar(e, a.level, 2, bp(a), k.data(), true, bp(o), batch);
+        Ct o = make(a.level, a.nb);
+        op_scalar(e, a.level, 2, bp(a), k.data(), true, bp(o), a.nb);
         return o;
     }
     // pointer table [term][batch] on the device; the table itself is freed in stream order
@@ -179,20 +196,20 @@ struct DevOps {
         return d;
     }
     Ct sum_terms(const std::vector<const Ct*>& cts, const std::vector<const Pt*>& pts) {
-        const int lv = cts[0]->level, n_mac = (int)pts.size(), n_all = (int)cts.size();
-        Ct o = make(lv);
-        std::vector<const u64*> tab((size_t)(n_all + n_mac + 1) * batch);
+        const int lv = cts[0]->level, n_mac = (int)pts.size(), n_all = (int)cts.size(), nbat = cts[0]->nb;
+        Ct o = make(lv, nbat);
+        std::vector<const u64*> tab((size_t)(n_all + n_mac + 1) * nbat);
         for (int t = 0; t < n_all; t++) {
             LSB_CHECK(cts[t]->level == lv, "lsb bootstrap: sum operands at different levels");
-            for (int b = 0; b < batch; b++) tab[(size_t)t * batch + b] = cts[t]->p + (size_t)b * words(lv);
+            for (int b = 0; b < nbat; b++) tab[(size_t)t * nbat + b] = cts[t]->p + (size_t)b * words(lv);
         }
         for (int t = 0; t < n_mac; t++) {
             LSB_CHECK(pts[t]->level == lv, "lsb bootstrap: plaintext at the wrong level");
-            for (int b = 0; b < batch; b++) tab[(size_t)(n_all + t) * batch + b] = pts[t]->p;
+            for (int b = 0; b < nbat; b++) tab[(size_t)(n_all + t) * nbat + b] = pts[t]->p;
         }
-        for (int b = 0; b < batch; b++) tab[(size_t)(n_all + n_mac) * batch + b] = o.p + (size_t)b * words(lv);
+        for (int b = 0; b < nbat; b++) tab[(size_t)(n_all + n_mac) * nbat + b] = o.p + (size_t)b * words(lv);
         const u64** d = upload_table(tab);
-        op_sum_terms(e, lv, 2, d, d + (size_t)n_all * batch, (u64* const*)(d + (size_t)(n_all + n_mac) * batch), n_mac, n_all - n_mac, batch);
+        op_sum_terms(e, lv, 2, d, d + (size_t)n_all * nbat, (u64* const*)(d + (size_t)(n_all + n_mac) * nbat), n_mac, n_all - n_mac, nbat);
         LSB_CUDA(cudaFreeAsync((void*)d, e.s));
         return o;
     }
@@ -228,7 +245,7 @@ void DeviceBootstrap::run(Workspace& ws, cudaStream_t s, const BootstrapKeys& ke
     OpEnv e{ctx_, ws, s, 0};
     DevOps ops(e, batch, keys, impl_->owned);
     // gather the batch (independently allocated level-0 ciphertexts) into one block
-    DevOps::Ct ct0 = ops.make(0);
+    DevOps::Ct ct0 = ops.make(0, batch);
     op_drop_to(e, 0, 0, 2, in, ops.bp(ct0), batch);
     impl_->B.st = {};
     DevOps::Ct res = impl_->B.run(ops, ct0);

@@ -13,7 +13,8 @@ using orc::u64;
 struct OracleOps {
     struct Ct {
         int level = -1;
-        std::vector<u64> d;  // [batch][2][level+1][N]
+        int nb = 0;          // batch items held (the pipeline stacks two batches for EvalMod)
+        std::vector<u64> d;  // [nb][2][level+1][N]
     };
     struct Pt {
         int level = -1;
@@ -31,11 +32,24 @@ struct OracleOps {
     OracleOps(const orc::Context& ctx, int batch_) : c(ctx), batch(batch_), N(ctx.N) {}
     int level(const Ct& a) const { return a.level; }
     size_t words(int level) const { return (size_t)2 * (level + 1) * N; }
-    Ct make(int level) const {
+    Ct make(int level, int nb) const {
         Ct o;
         o.level = level;
-        o.d.assign(words(level) * batch, 0);
+        o.nb = nb;
+        o.d.assign(words(level) * nb, 0);
         return o;
+    }
+    Ct concat(const Ct& a, const Ct& b) const {
+        Ct o = make(a.level, a.nb + b.nb);
+        std::memcpy(o.d.data(), a.d.data(), a.d.size() * sizeof(u64));
+        std::memcpy(o.d.data() + a.d.size(), b.d.data(), b.d.size() * sizeof(u64));
+        return o;
+    }
+    std::pair<Ct, Ct> split(const Ct& c) const {
+        Ct a = make(c.level, c.nb / 2), b = make(c.level, c.nb - c.nb / 2);
+        std::memcpy(a.d.data(), c.d.data(), a.d.size() * sizeof(u64));
+        std::memcpy(b.d.data(), c.d.data() + a.d.size(), b.d.size() * sizeof(u64));
+        return {std::move(a), std::move(b)};
     }
     Pt make_plain(int level, const std::vector<u64>& coeff) const {
         Pt p;
@@ -54,8 +68,8 @@ struct OracleOps {
     Ct rotate_gal(const Ct& a, u64 gal) const {
         auto it = glk.find(gal);
         if (it == glk.end()) throw std::runtime_error("btp oracle: no Galois key for element " + std::to_string(gal));
-        Ct o = make(a.level);
-        for (int b = 0; b < batch; b++)
+        Ct o = make(a.level, a.nb);
+        for (int b = 0; b < a.nb; b++)
             orc::ckks_rotate(c, a.level, &a.d[words(a.level) * b], it->second, key_level, gal, &o.d[words(a.level) * b]);
         return o;
     }
@@ -68,9 +82,9 @@ struct OracleOps {
     }
     Ct switch_key(const Ct& a, int which) const {
         const int l = a.level + 1;
-        Ct o = make(a.level);
+        Ct o = make(a.level, a.nb);
         std::vector<u64> p0((size_t)l * N), p1((size_t)l * N);
-        for (int b = 0; b < batch; b++) {
+        for (int b = 0; b < a.nb; b++) {
             const u64* ct = &a.d[words(a.level) * b];
             u64* out = &o.d[words(a.level) * b];
             orc::keyswitch_ntt(c, a.level, ct + (size_t)l * N, swk[which], swk_level[which], p0.data(), p1.data());
@@ -86,10 +100,10 @@ struct OracleOps {
     }
     Ct mod_raise(const Ct& a, int top) const {
         if (a.level != 0) throw std::runtime_error("btp oracle: mod_raise expects level 0");
-        Ct o = make(top);
+        Ct o = make(top, a.nb);
         const u64 q0 = c.Q(0).q;
         std::vector<u64> co(N);
-        for (int b = 0; b < batch; b++)
+        for (int b = 0; b < a.nb; b++)
             for (int p = 0; p < 2; p++) {
                 std::memcpy(co.data(), &a.d[words(0) * b + (size_t)p * N], N * sizeof(u64));
                 orc::ntt_inverse(c.Q(0), c.N, co.data());
@@ -106,42 +120,42 @@ struct OracleOps {
         return o;
     }
     Ct add(const Ct& a, const Ct& b) const {
-        Ct o = make(a.level);
-        for (int i = 0; i < batch; i++) orc::ct_add(c, a.level, 2, &a.d[words(a.level) * i], &b.d[words(a.level) * i], &o.d[words(a.level) * i]);
+        Ct o = make(a.level, a.nb);
+        for (int i = 0; i < a.nb; i++) orc::ct_add(c, a.level, 2, &a.d[words(a.level) * i], &b.d[words(a.level) * i], &o.d[words(a.level) * i]);
         return o;
     }
     Ct sub(const Ct& a, const Ct& b) const {
-        Ct o = make(a.level);
-        for (int i = 0; i < batch; i++) orc::ct_sub(c, a.level, 2, &a.d[words(a.level) * i], &b.d[words(a.level) * i], &o.d[words(a.level) * i]);
+        Ct o = make(a.level, a.nb);
+        for (int i = 0; i < a.nb; i++) orc::ct_sub(c, a.level, 2, &a.d[words(a.level) * i], &b.d[words(a.level) * i], &o.d[words(a.level) * i]);
         return o;
     }
     Ct mul_relin(const Ct& a, const Ct& b) const {
-        Ct o = make(a.level);
+        Ct o = make(a.level, a.nb);
         std::vector<u64> t3((size_t)3 * (a.level + 1) * N);
-        for (int i = 0; i < batch; i++) {
+        for (int i = 0; i < a.nb; i++) {
             orc::ckks_mult(c, a.level, &a.d[words(a.level) * i], &b.d[words(a.level) * i], t3.data());
             orc::ckks_relin(c, a.level, t3.data(), rlk, key_level, &o.d[words(a.level) * i]);
         }
         return o;
     }
     Ct rescale(const Ct& a) const {
-        Ct o = make(a.level - 1);
-        for (int i = 0; i < batch; i++) orc::ckks_rescale(c, a.level, 2, &a.d[words(a.level) * i], &o.d[words(a.level - 1) * i]);
+        Ct o = make(a.level - 1, a.nb);
+        for (int i = 0; i < a.nb; i++) orc::ckks_rescale(c, a.level, 2, &a.d[words(a.level) * i], &o.d[words(a.level - 1) * i]);
         return o;
     }
     Ct drop_to(const Ct& a, int level) const {
         if (level == a.level) return a;
-        Ct o = make(level);
-        for (int i = 0; i < batch; i++)
+        Ct o = make(level, a.nb);
+        for (int i = 0; i < a.nb; i++)
             for (int p = 0; p < 2; p++)
                 std::memcpy(&o.d[words(level) * i + (size_t)p * (level + 1) * N], &a.d[words(a.level) * i + (size_t)p * (a.level + 1) * N],
                             (size_t)(level + 1) * N * sizeof(u64));
         return o;
     }
     Ct mul_scalar(const Ct& a, const std::vector<u64>& k) const {
-        Ct o = make(a.level);
+        Ct o = make(a.level, a.nb);
         const int l = a.level + 1;
-        for (size_t r = 0; r < (size_t)batch * 2 * l; r++) {
+        for (size_t r = 0; r < (size_t)a.nb * 2 * l; r++) {
             const int i = (int)(r % l);
             const u64 q = c.Q(i).q;
             for (size_t x = 0; x < N; x++) o.d[r * N + x] = orc::mulmod(a.d[r * N + x], k[i], q);
@@ -151,7 +165,7 @@ struct OracleOps {
     Ct add_scalar(const Ct& a, const std::vector<u64>& k) const {
         Ct o = a;
         const int l = a.level + 1;
-        for (int b = 0; b < batch; b++)
+        for (int b = 0; b < a.nb; b++)
             for (int i = 0; i < l; i++) {
                 const u64 q = c.Q(i).q;
                 u64* p = &o.d[words(a.level) * b + (size_t)i * N];
@@ -161,9 +175,9 @@ struct OracleOps {
     }
     Ct sum_products(const std::vector<const Ct*>& cts, const std::vector<const Pt*>& pts) const {
         const int lv = cts[0]->level, l = lv + 1;
-        Ct o = make(lv);
+        Ct o = make(lv, cts[0]->nb);
         for (size_t t = 0; t < cts.size(); t++)
-            for (size_t r = 0; r < (size_t)batch * 2 * l; r++) {
+            for (size_t r = 0; r < (size_t)cts[0]->nb * 2 * l; r++) {
                 const int i = (int)(r % l);
                 const u64 q = c.Q(i).q;
                 const u64* pt = &pts[t]->d[(size_t)i * N];
@@ -227,7 +241,7 @@ int btp_oracle_run(const int* ip, const double* dp, const u64* q, int nq, const 
         ops.swk[1] = swk_std;
         ops.swk_level[0] = 0;
         ops.swk_level[1] = key_level;
-        OracleOps::Ct in = ops.make(0);
+        OracleOps::Ct in = ops.make(0, batch);
         std::memcpy(in.d.data(), ct0, in.d.size() * sizeof(u64));
         OracleOps::Ct res = B.run(ops, in);
         if (res.level != P.out_level) throw std::runtime_error("btp oracle: unexpected output level");

@@ -49,6 +49,9 @@ inline BatchPtr bp_offset(BatchPtr p, size_t words) {
 
 // Rows (limbs) of one batch item a kernel works on: slot = limb offset (in units of N words)
 // inside the item's input / output block, mod = index into the context's modulus table.
+// Slots and modulus indices are uint8_t: a launch addresses at most kMaxRows = 192 limbs of one item and slot numbers stay
+// below 256 -- the largest user is the cfg5 key-switch, beta * (l + k) = 5 * 30 = 150 extended limbs (every builder checks
+// against kMaxRows; a parameter set with more than 255 limbs per item would need uint16_t here).
 constexpr int kMaxRows = 192;
 struct RowMap {
     int n;

@@ -420,8 +420,34 @@ def gen_reference_extras():
     emit("bfv8k_custom_at_end", [Argument("in_x_list", xs), Argument("in_y_list", ys)], [Argument("out_z_list", zs)])
 
 
+def gen_custom_start():
+    """Custom (host) nodes at the START of the graph feeding device nodes: unittests/test_gpu_bfv.py:570-647 (custom_cmpac /
+    custom_compute_at_start): custom data inputs -> `encode_ringt` / `encode` custom nodes -> plaintexts the device consumes."""
+    for tag, mkparam, Ct, PtR, Pt, lv in (("bfv8k", bfv8k, BfvCiphertextNode, BfvPlaintextRingtNode, BfvPlaintextNode, 2),
+                                          ("ckks8k", ckks8k, CkksCiphertextNode, CkksPlaintextRingtNode, CkksPlaintextNode, 4)):
+        set_fhe_param(mkparam())
+        xs = [Ct(f"x_{i}", level=lv) for i in range(7)]
+        ys = [CustomDataNode(type="msg", id=f"y_{i}", attributes={"level": 0}) for i in range(7)]
+        ys.append(CustomDataNode("y_7"))
+        prods = []
+        for i in range(7):
+            e = PtR(f"encoded_y_ringt_{i}")
+            custom_compute(inputs=[ys[i]], output=e, type="encode_ringt")
+            prods.append(mult(xs[i], e, f"mult_{i}"))
+        res = prods[0]
+        for i in range(1, 7):
+            res = add(res, prods[i], f"partial_sum_{i}")
+        last = Pt("encoded_y_last", level=res.level)
+        custom_compute(inputs=[ys[7]], output=last, type="encode", attributes={"level": res.level})
+        final = add(res, last, "z_final")
+        emit(f"{tag}_custom_cmpac", [Argument("in_x_list", xs), Argument("in_y_list", ys)], [Argument("out_z_list", final)])
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if sys.argv[1:] == ["custom"]:
+        gen_custom_start()
+        sys.exit(0)
     if sys.argv[1:] == ["btp"]:
         gen_bootstrap()
         sys.exit(0)

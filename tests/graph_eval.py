@@ -130,6 +130,17 @@ class GraphCase:
         self._pool = {}
         for idx in self.g["inputs"]:
             d = self.data[idx]
+            if d.get("is_custom"):
+                # custom payload consumed by an `encode_ringt` / `encode` custom node: generated in the shape of the
+                # plaintext that node outputs (the test plug-in's encoders are identity, tests/harness/harness.cpp)
+                cons = [c for c in self.compute.values() if idx in c["inputs"]][0]
+                od = self.data[cons["outputs"][0]]
+                if od["type"] == "pt_ringt":
+                    tt = self.params.t if self.params.scheme == R.SCHEME_BFV else 65537
+                    self.values[idx] = self.rng.integers(0, tt, size=(1, self.N), dtype=np.uint64)
+                else:
+                    self.values[idx] = self._rand_limbs((), q[:od["level"] + 1])
+                continue
             t, lv = d["type"], d["level"]
             if t in ("ct", "ct3") and self.btp is not None:
                 z = self.rng.uniform(-1, 1, self.N // 2) + 1j * self.rng.uniform(-1, 1, self.N // 2)
@@ -254,6 +265,8 @@ class GraphCase:
             out, self.btp_stats = B.oracle_bootstrap(o, self.btp, k, V[ins[0]][None])
             return out[0]
         if c.get("is_custom"):
+            if t in ("encode_ringt", "encode"):
+                return V[ins[0]]
             if t == "passthrough":
                 return V[ins[0]]
             raise ValueError("unknown custom node " + t)
@@ -293,6 +306,9 @@ class GraphCase:
         keep.append(arr)
         h.n, h.k = self.N, len(self.params.p)
         h.data = arr.ctypes.data_as(C.POINTER(C.c_uint64))
+        if d.get("is_custom"):
+            h.level, h.degree, h.kind = arr.shape[0] - 1, 0, 5
+            return h
         h.level, h.degree = d["level"], d.get("degree", 0)
         h.kind = {"ct": 0, "ct3": 0, "pt": 1, "pt_mul": 1, "pt_ringt": 2, "rlk": 3, "swk": 3, "glk": 3}[t]
         return h
@@ -302,7 +318,7 @@ class GraphCase:
         list (each `size` handles), then rlk, then ONE glk handle (cxx_sdk_v2/cxx_argument.h:178-260)."""
         keep = []
         in_ids = list(self.g["inputs"])
-        data_ids = [i for i in in_ids if self.data[i]["type"] not in ("rlk", "glk", "swk")]
+        data_ids = [i for i in in_ids if self.data[i].get("is_custom") or self.data[i]["type"] not in ("rlk", "glk", "swk")]
         args_in, handles_in = [], []
         pos = 0
         for a in self.sig["online"]:
@@ -311,13 +327,14 @@ class GraphCase:
             cnt = int(np.prod(a["size"]))
             ids = data_ids[pos:pos + cnt]
             pos += cnt
-            ty = TYPE_CIPHERTEXT if a["type"] in ("ct", "ct3") else TYPE_PLAINTEXT
-            args_in.append((ty, a["level"], cnt))
+            is_custom = any(self.data[i].get("is_custom") for i in ids)
+            ty = TYPE_CUSTOM if is_custom else TYPE_CIPHERTEXT if a["type"] in ("ct", "ct3") else TYPE_PLAINTEXT
+            args_in.append((ty, a.get("level", 0), cnt))
             for i in ids:
                 handles_in.append(self._handle(i, self.values[i], keep))
         assert pos == len(data_ids), "task_signature does not cover the data inputs"
         for i in in_ids:
-            if self.data[i]["type"] == "rlk":
+            if not self.data[i].get("is_custom") and self.data[i]["type"] == "rlk":
                 args_in.append((TYPE_RELIN_KEY, self.data[i]["level"], 1))
                 handles_in.append(self._handle(i, self.values[i], keep))
         if self.glk:
@@ -337,7 +354,7 @@ class GraphCase:
             args_in.append((TYPE_GALOIS_KEY, -1, 1))
             handles_in.append(hs)
         for i in in_ids:
-            if self.data[i]["type"] == "swk":
+            if not self.data[i].get("is_custom") and self.data[i]["type"] == "swk":
                 args_in.append((TYPE_SWITCH_KEY, self.data[i]["level"], 1))
                 handles_in.append(self._handle(i, self.values[i], keep))
         args_out, handles_out, outs = [], [], []

@@ -22,7 +22,8 @@ extern "C" const char* lsb_gpu_task_last_error(void);
 extern "C" {
 // one frontend handle (mirrors what BfvCiphertext / CkksPlaintext / RelinKey / GaloisKey handles carry)
 struct THandle {
-    int kind;     // 0 ciphertext, 1 plaintext (pt / pt_mul: level+1 limbs), 2 pt_ringt (1 limb), 3 key-switch key, 4 Galois key set
+    int kind;     // 0 ciphertext, 1 plaintext (pt / pt_mul: level+1 limbs), 2 pt_ringt (1 limb), 3 key-switch key, 4 Galois key set,
+                  // 5 custom payload (a message: `level+1` rows of n words, what a CustomData handle carries)
     int level;    // ciphertext/plaintext level, or key level
     int degree;   // ciphertext degree
     int n;        // ring degree
@@ -138,6 +139,10 @@ ExecutorFunc make_export() {
                 });
                 break;
             }
+            case TYPE_CUSTOM:  // custom data input: handed on as it is (mega_ag.cpp:424-434, "Case 0"; the SDK returns shared_ptr<CustomData>)
+                if (h->kind != 5) throw std::runtime_error("harness: custom payload handle expected for node " + d->id);
+                output = std::shared_ptr<THandle>(h, [](THandle*) {});
+                break;
             default: throw std::runtime_error("harness: unsupported data type for EXPORT_TO_ABI");
         }
     };
@@ -203,6 +208,33 @@ ExecutorFunc make_passthrough(bool add_one) {
     };
 }
 
+// custom nodes "encode_ringt" / "encode" (unittests/test_gpu_bfv.cpp:1109-1131): a custom payload (kind 5) becomes a
+// pt_ringt / plaintext handle the device consumes through EXPORT_TO_ABI; the payload is taken as already encoded (the
+// test plug-in has no encoder), `encode` reads its level from the node's attributes like the reference executor does
+ExecutorFunc make_encode(bool ringt) {
+    return [ringt](ExecutionContext&, const std::unordered_map<NodeIndex, std::any>& inputs, std::any& output, const ComputeNode& self) {
+        const DatumNode* d = self.input_nodes[0];
+        std::shared_ptr<THandle> owner;
+        THandle* src = handle_of(d, inputs.at(d->index), &owner);
+        if (!src || src->kind != 5) throw std::runtime_error("harness: encode expects a custom payload handle");
+        int level = 0;
+        if (!ringt) {
+            if (!self.custom_prop.has_value()) throw std::runtime_error("harness: custom property not found for encode");
+#ifdef LATTISENSE_WITH_NLOHMANN_JSON
+            level = self.custom_prop->attributes.at("level").get<int>();
+#else
+            level = self.custom_prop->attributes.at("level").as_int();
+#endif
+        }
+        if (src->level != level) throw std::runtime_error("harness: payload rows do not match the encode level");
+        g_custom_calls++;
+        THandle* h = new THandle(*src);
+        h->kind = ringt ? 2 : 1;
+        h->level = level;
+        output = std::shared_ptr<THandle>(h);  // non-owning view of the payload's words
+    };
+}
+
 struct Progress {
     std::atomic<int> calls{0};
     std::atomic<int> last_completed{0};
@@ -229,10 +261,10 @@ void* th_open(const char* project_path, int bind_executors) {
             // executors are copied by the callee: locals may die right after the call (plug-in/lattigo/acc/gpu_runner.go:94-96)
             ExecutorFunc ex = make_export(), im = make_import();
             bind_gpu_task_abi_bridge_executors(t, &ex, &im);
-            ExecutorFunc pass = make_passthrough(false);
-            const char* types[1] = {"passthrough"};
-            void* fns[1] = {&pass};
-            bind_gpu_task_custom_executors(t, types, fns, 1);
+            ExecutorFunc pass = make_passthrough(false), er = make_encode(true), en = make_encode(false);
+            const char* types[3] = {"passthrough", "encode_ringt", "encode"};
+            void* fns[3] = {&pass, &er, &en};
+            bind_gpu_task_custom_executors(t, types, fns, 3);
         }
         return t;
     } catch (const std::exception& e) {

@@ -73,6 +73,19 @@ int lsb_rescale(lsb_context_t ctx, int level, int npoly, const uint64_t* d_in, u
  * ciphertext [npoly][1][N] -> [npoly][top_level+1][N], the centred residues mod q_0 re-read modulo every prime. */
 int lsb_mod_raise(lsb_context_t ctx, int top_level, int npoly, const uint64_t* d_in, uint64_t* d_out, int batch,
                   void* stream);
+/* lsb_mod_raise without any device allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arguments, same kernels and bit-identical output as lsb_mod_raise; the INTT's intermediate
+ * (npoly * N * batch words) lives in a file-scope `static __device__` array of LSB_STATIC_SCRATCH_WORDS 64-bit words
+ * (4 MiB, held by every GPU that loads the library until the process exits) instead of the context's workspace.
+ * Returns 1 with a message in lsb_last_error() when npoly * N * batch > LSB_STATIC_SCRATCH_WORDS (split the batch, or
+ * call lsb_mod_raise).  The call itself makes no cudaMalloc / cudaFree / stream-ordered allocation; its first use on a
+ * device resolves the array's address with cudaGetSymbolAddress.  All calls on a device share the array, which keeps the
+ * previous call's contents (ModRaise overwrites what it reads, nothing is cleared): calls whose kernels overlap on the
+ * GPU -- different streams with no ordering between them -- race; keep them ordered. */
+#define LSB_STATIC_SCRATCH_WORDS (1u << 19)
+int lsb_mod_raise_static(lsb_context_t ctx, int top_level, int npoly, const uint64_t* d_in, uint64_t* d_out, int batch,
+                         void* stream);
 /* Diagonal-form linear transform, baby-step / giant-step: the CoeffsToSlots / SlotsToCoeffs matrices of CKKS
  * bootstrapping (rotation sets: frontend/bootstrap_params.py:159-209).  diag_rot[i] = diagonal index k_i;
  * d_diag_pt[i] = its plaintext [level+1][N], NTT domain, slot values rotated by -(k_i - k_i mod n1) at encode time;

@@ -60,6 +60,7 @@ def lib():
     L.lsb_rescale.argtypes = [vp, ci, ci, vp, vp, ci, vp]
     L.lsb_drop_level.argtypes = [vp, ci, ci, vp, vp, ci, vp]
     L.lsb_mod_raise.argtypes = [vp, ci, ci, vp, vp, ci, vp]
+    L.lsb_mod_raise_static.argtypes = [vp, ci, ci, vp, vp, ci, vp]
     L.lsb_linear_transform.argtypes = [vp, ci, vp, ci, vp, vp, ci, ci, vp, vp, ci, vp, vp]
     L.lsb_rotate.argtypes = [vp, ci, vp, vp, ci, C.c_uint64, vp, ci, vp]
     L.lsb_add.argtypes = [vp, ci, ci, vp, vp, vp, ci, vp]
@@ -98,6 +99,9 @@ def lib():
     L.lsb_profile_read.argtypes = [vp, ci, C.POINTER(C.c_double), C.POINTER(C.c_longlong), C.POINTER(C.c_double)]
     _lib = L
     return L
+
+
+STATIC_SCRATCH_WORDS = 1 << 19  # LSB_STATIC_SCRATCH_WORDS (include/lsb200.h)
 
 
 def _check(rc):
@@ -270,6 +274,11 @@ class Context:
         r = self._run(lambda bf, o: _check(lib().lsb_mod_raise(self.h, top_level, npoly, bf[0].ptr, o.ptr, B, self.stream)),
                       [ct0], (B, npoly, top_level + 1, N))
         return r[0] if single else r
+
+    def mod_raise_static_dev(self, top_level, npoly, d_in, d_out, batch):
+        """lsb_mod_raise_static on caller-owned device buffers: ModRaise that allocates nothing (scratch in the library's
+        static device array of STATIC_SCRATCH_WORDS words; no counterpart in the reference)."""
+        _check(lib().lsb_mod_raise_static(self.h, top_level, npoly, d_in.ptr, d_out.ptr, batch, self.stream))
 
     def linear_transform(self, ct, plan, n1, keys):
         """BSGS diagonal-form linear transform + rescale (lsb_linear_transform).  plan: [(diagonal index k, plaintext

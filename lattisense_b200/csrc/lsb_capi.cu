@@ -20,6 +20,8 @@ Context& lsb_context_ref(lsb_context_t h) {  // for the other translation units 
     return *h->c;
 }
 
+void lsb_set_last_error(const std::string& what) { g_err = what; }  // for lsb_noalloc.cu
+
 #define LSB_API_BEGIN \
     g_err.clear();    \
     try {

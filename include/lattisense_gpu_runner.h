@@ -125,6 +125,11 @@ int run_fhe_gpu_task(fhe_task_handle handle, CArgument* input_args, uint64_t n_i
 /* Devices used by the NEXT run of this task: independent components of the DAG are sharded over
  * devices[0..n).  Default: the single `gpu_device` passed to run_fhe_gpu_task. */
 void lsb_gpu_task_set_devices(fhe_task_handle handle, const int* devices, int n_devices);
+/* The list is a request: a device is opened only per LSB_MIN_WEIGHT_PER_DEVICE (environment, default 800 = about 200 key
+ * switches at n = 16384; 0 = always use every device) of work in the graph and never for more devices than the graph has
+ * independent components, because each device costs a copy of the keys and a shorter launch train (cfg3 x 64 on B200s:
+ * 11.7 ms on 4 devices, 15.5 ms on 8).  Returns how many of `n_devices` the next run would use (the first ones listed). */
+int lsb_gpu_task_worthwhile_devices(fhe_task_handle handle, int n_devices);
 /* Message of the last failed run_fhe_gpu_task on the calling thread ("" if none). */
 const char* lsb_gpu_task_last_error(void);
 /* Statistics of the last run: kernel launches, batched launch groups, nodes fused away. */

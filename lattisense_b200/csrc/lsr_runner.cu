@@ -257,6 +257,11 @@ struct DeviceRuntime {
         if (h2d) cudaStreamDestroy(h2d);
         for (auto st : h2d_extra) cudaStreamDestroy(st);
         if (d2h) cudaStreamDestroy(d2h);
+        // the release threshold of the stream-ordered pool is "never" while tasks run (blocks are recycled across runs);
+        // a released task hands its cached blocks back, so that a process that goes on to other work on this device does
+        // not allocate out of a pool fragmented into this task's object sizes
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0);
     }
 };
 
@@ -616,6 +621,22 @@ static std::vector<int> assign_components(const Plan& p, int n_slots) {
     return slot_of;
 }
 
+// How many of the `n_slots` devices a run should open.  Every extra device costs a replica of the keys it needs (one H2D
+// each), a dispatcher and shorter launch trains; measured on B200s with cfg3 x 64 (64 components, total weight ~3.8 k):
+// 21.9 / 15.3 / 11.7 ms on 1 / 2 / 4 devices but 15.5 ms on 8.  A device is therefore opened only per
+// LSB_MIN_WEIGHT_PER_DEVICE (default 800, about 200 key switches at n = 16384; scaled with the ring degree) of
+// component weight, and never for more devices than there are components.  The first `result` devices of the list are used.
+static int worthwhile_slots(const Plan& p, int n_slots, double ring_n) {
+    if (n_slots <= 1) return std::max(1, n_slots);
+    const char* env = getenv("LSB_MIN_WEIGHT_PER_DEVICE");  // read per run: tests turn the cap off with 0
+    const double min_w = env ? std::max(0.0, atof(env)) : 800.0;
+    double total = 0.0;
+    for (double w : p.component_weight) total += w;
+    total *= std::max(1.0, ring_n / 16384.0);
+    int use = min_w > 0.0 ? (int)(total / min_w) : n_slots;
+    use = std::min(use, p.n_components);
+    return std::max(1, std::min(use, n_slots));
+}
 
 // ---------------------------------------------------------------------------------------------
 // the task object behind fhe_task_handle
@@ -1760,6 +1781,7 @@ static int run_task(GpuTask& task, CArgument* input_args, uint64_t n_in, CArgume
     std::lock_guard<std::mutex> run_lock(task.run_mu);
     TaskGraph& g = *task.graph;
     std::vector<int> devs = task.devices.empty() ? std::vector<int>{gpu_device} : task.devices;
+    devs.resize(worthwhile_slots(task.plan, (int)devs.size(), (double)g.param.n));
     const int hw = (int)std::thread::hardware_concurrency();
     // worker threads: the copies they make are bound by host DRAM bandwidth, not by cores -- measured on a 16-core B200
     // host (cfg2 x1024 through run_fhe_gpu_task, profiles/r02_e2e_host_path.txt): 8 threads 62 ms, 12 threads 65 ms,
@@ -2050,6 +2072,13 @@ int lsb_gpu_task_shard_preview(fhe_task_handle handle, int n_slots, int* slot_of
     std::vector<int> s = lsr::assign_components(t->plan, n_slots);
     for (int i = 0; i < (int)s.size() && i < capacity; i++) slot_of_component[i] = s[i];
     return (int)s.size();
+}
+
+// how many of `n_devices` the next run would open (lsb_gpu_task_set_devices is a request: small graphs use fewer)
+int lsb_gpu_task_worthwhile_devices(fhe_task_handle handle, int n_devices) {
+    GpuTask* t = reinterpret_cast<GpuTask*>(handle);
+    if (!t) return -1;
+    return lsr::worthwhile_slots(t->plan, n_devices, (double)t->graph->param.n);
 }
 
 }  // extern "C"

@@ -80,6 +80,29 @@ def test_components_and_sharding_cfg2():
         h.th_close(t)
 
 
+def test_small_graphs_open_fewer_devices(monkeypatch, tmp_path):
+    """lsb_gpu_task_set_devices is a request: 8 small components stay on one device, cfg3 x 64 uses 4 of 8 (the measured
+    optimum), and the cap can be switched off"""
+    lib = GE.runner_lib()
+    lib.lsb_gpu_task_worthwhile_devices.argtypes = [C.c_void_p, C.c_int]
+    monkeypatch.delenv("LSB_MIN_WEIGHT_PER_DEVICE", raising=False)
+    h = GE.harness()
+    for case, want in (("cfg2_ckks_mult_x8", {1: 1, 2: 1, 8: 1}), ("cfg3_bfv_poly7_x64", {1: 1, 2: 2, 4: 4, 8: 4})):
+        path = os.path.join(GE.GRAPHS, case)
+        if not os.path.exists(os.path.join(path, "mega_ag.json")):  # large fixtures are committed gzipped
+            path = GE.unpack_case(case, str(tmp_path))
+        t = h.th_open(path.encode(), 1)
+        assert t, h.th_last_error().decode()
+        try:
+            for n, w in want.items():
+                assert lib.lsb_gpu_task_worthwhile_devices(t, n) == w, (case, n)
+            monkeypatch.setenv("LSB_MIN_WEIGHT_PER_DEVICE", "0")
+            assert lib.lsb_gpu_task_worthwhile_devices(t, 8) == 8
+            monkeypatch.delenv("LSB_MIN_WEIGHT_PER_DEVICE")
+        finally:
+            h.th_close(t)
+
+
 def test_custom_node_splits_device_path():
     h, t, d = _describe("bfv8k_custom_in_middle")
     try:

@@ -6,7 +6,7 @@ sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 import ctypes as C, numpy as np, torch
 import fhe_ref as R, lattisense_b200 as L, btp_ref as BT
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 1
-P = R.CKKS_BTP_N16; dev = torch.device("cuda", 0)
+P = getattr(R, os.environ.get("BTP_PARAMS", "CKKS_BTP_N16")); dev = torch.device("cuda", 0)
 ctx = L.Context(P.scheme, P.logN, P.q, P.p, 0); st = torch.cuda.current_stream().cuda_stream; ctx.stream = st; lib = L.lib()
 def limbs(lead, mods):
     t = torch.empty(lead + (len(mods), P.N), dtype=torch.int64, device=dev)
@@ -26,6 +26,6 @@ e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=Tr
 t0 = time.perf_counter(); e0.record()
 for _ in range(3): run()
 e1.record(); t_host = (time.perf_counter() - t0) / 3; torch.cuda.synchronize()
-print("bootstrap n=65536 batch %d hoist=%s: %.2f ms per call (host enqueue %.2f ms), launches per call %d" % (B, os.environ.get("LSB_BTP_HOIST", "1"), e0.elapsed_time(e1) / 3, t_host * 1e3, 0))
+print("bootstrap n=%d batch %d hoist=%s: %.2f ms per call (host enqueue %.2f ms), launches per call %d" % (P.N, B, os.environ.get("LSB_BTP_HOIST", "1"), e0.elapsed_time(e1) / 3, t_host * 1e3, 0))
 n0 = ctx.launch_count(); ctx.profile(True); run(); torch.cuda.synchronize()
 print("   launches", ctx.launch_count() - n0, {k: round(ctx.profile_read(i)[0], 2) for i, k in enumerate(["ntt_fwd", "ntt_inv", "basis_ext", "ks_inner", "elementwise"])})

@@ -20,7 +20,9 @@ __global__ void __launch_bounds__(1024) k(u64* out, u64 seed, u64 q) {
 #pragma unroll
     for (int i = 0; i < ILP; i++) a32[i] = (u32)x[i];
     const u64 w = seed * 0x9E3779B97F4A7C15ull % q, ws = (u64)(((unsigned __int128)w << 64) / q);
-    const u64 q2 = 2 * q;
+    const u64 q2 = 2 * q, q4 = 4 * q;
+    const u32 w1p = (u32)(ws >> 32);
+    const double dw0s = (double)(u32)ws * 2.3283064365386963e-10, dw1s = (double)w1p * 2.3283064365386963e-10;  // * 2^-32
     double d[ILP];
 #pragma unroll
     for (int i = 0; i < ILP; i++) d[i] = (double)(x[i] & 0xffffffffffull);
@@ -81,6 +83,40 @@ __global__ void __launch_bounds__(1024) k(u64* out, u64 seed, u64 q) {
                     x[i - 1] = XX + T;
                     x[i] = XX - T + q2;
                 }
+            } else if (KIND == 12) {  // hybrid Shoup multiply: the high product's cross terms on the FP64 pipe
+                // y*w' / 2^64 = y1*w1' + (y1*w0' + y0*w1') / 2^32 + y0*w0' / 2^64: the first term exact (one IMAD.WIDE), the
+                // middle one floor-rounded in two DFMA.RM on the 2^52 grid, the last dropped: qhat in [Qshoup - 2, Qshoup],
+                // r = y*w - qhat*q in [0, 4q)
+                const u32 y0 = (u32)x[i], y1 = (u32)(x[i] >> 32);
+                const double dy1 = __hiloint2double(0x43300000, (int)y1) - 4503599627370496.0;
+                const double dy0 = __hiloint2double(0x43300000, (int)y0) - 4503599627370496.0;
+                double f = __fma_rd(dy1, dw0s, 4503599627370496.0);
+                f = __fma_rd(dy0, dw1s, f);
+                const u64 bt = (u64)__double_as_longlong(f) & 0xFFFFFFFFFFFFFull;
+                const u64 qh = (u64)y1 * w1p + bt;
+                x[i] = x[i] * w - qh * q;
+            } else if (KIND == 13) {  // one IMAD.WIDE and one DFMA per slot, independent chains: do the two pipes overlap?
+                x[i] = (u64)(u32)x[i] * b32 + x[i];
+                d[i] = fma(d[i], dw, dq);
+            } else if (KIND == 14) {  // hybrid butterfly, values in [0, 8q), one conditional subtraction of 4q
+                if (i & 1) {
+                    u64 X = x[i - 1], Y = x[i];
+                    X = X >= q4 ? X - q4 : X;
+                    const u32 y0 = (u32)Y, y1 = (u32)(Y >> 32);
+                    const double dy1 = __hiloint2double(0x43300000, (int)y1) - 4503599627370496.0;
+                    const double dy0 = __hiloint2double(0x43300000, (int)y0) - 4503599627370496.0;
+                    double f = __fma_rd(dy1, dw0s, 4503599627370496.0);
+                    f = __fma_rd(dy0, dw1s, f);
+                    const u64 bt = (u64)__double_as_longlong(f) & 0xFFFFFFFFFFFFFull;
+                    const u64 qh = (u64)y1 * w1p + bt;
+                    const u64 T = Y * w - qh * q;
+                    x[i - 1] = X + T;
+                    x[i] = X - T + q4;
+                }
+            } else if (KIND == 15) {  // two IMAD.WIDE per DFMA
+                x[i] = (u64)(u32)x[i] * b32 + x[i];
+                x[i] = (u64)(u32)x[i] * c32 + x[i];
+                d[i] = fma(d[i], dw, dq);
             } else if (KIND == 8) {  // uncorrected lazy butterfly
                 if (i & 1) {
                     u64 X = x[i - 1], Y = x[i];
@@ -143,5 +179,9 @@ int main() {
     run<9>("DFMA", ILP, d, p.multiProcessorCount, mhz);
     run<10>("FP64 lazy butterfly", ILP / 2, d, p.multiProcessorCount, mhz);
     run<11>("FP64 + integer butterfly pair", ILP / 2, d, p.multiProcessorCount, mhz);
+    run<12>("hybrid Shoup mulmod (FP64 cross terms)", ILP, d, p.multiProcessorCount, mhz);
+    run<14>("hybrid butterfly [0,8q)", ILP / 2, d, p.multiProcessorCount, mhz);
+    run<13>("IMAD.WIDE + DFMA, independent", ILP, d, p.multiProcessorCount, mhz);
+    run<15>("2 IMAD.WIDE + DFMA, independent", ILP, d, p.multiProcessorCount, mhz);
     return 0;
 }

@@ -472,6 +472,28 @@ def run_ours(args):
             c16.h, l25 - 1, c3.data_ptr(), rk.data_ptr(), l25 - 1, o2.data_ptr(), B25, stream)), B25)
         del c3, rk, o2
         c16.close()
+        # the reference frontend's own default CKKS sets for n = 32768 and n = 65536 (frontend/parameter.json) at their top
+        # level: mult_relin_rescale and rotate ("N = 2^14..2^16" of BASELINE.json's metric; 41/46-bit Q primes on the FP64
+        # policy, 51/56-bit q0 and P primes on the integer policy; parity: tests/test_gpu_parity.py
+        # test_keyswitch_with_more_digits_than_one_launch_group)
+        for Pd, Bd in ((R.CKKS_N15, 64), (R.CKKS_N16, 16)):
+            try:
+                cd = L.Context(Pd.scheme, Pd.logN, Pd.q, Pd.p, 0, device=local)
+                cd.stream = stream
+                ld = len(Pd.q)
+                xa, xb = limbs((Bd, 2), Pd.q, Pd.N), limbs((Bd, 2), Pd.q, Pd.N)
+                kd = limbs((Pd.beta(ld - 1), 2), Pd.q + Pd.p, Pd.N)
+                xo = torch.empty((Bd, 2, ld - 1, Pd.N), dtype=torch.int64, device=dev)
+                secondary["ckks_mult_relin_rescale_n%d_level%d_ops_per_s" % (Pd.N, ld - 1)] = rate(lambda: L._check(
+                    lib.lsb_mult_relin_rescale(cd.h, ld - 1, xa.data_ptr(), xb.data_ptr(), kd.data_ptr(), ld - 1, xo.data_ptr(), Bd,
+                                               stream)), Bd, steps=3)
+                gd = R.galois_for_col_step(Pd.N, 1)
+                secondary["ckks_rotate_n%d_level%d_ops_per_s" % (Pd.N, ld - 1)] = rate(lambda: L._check(lib.lsb_rotate(
+                    cd.h, ld - 1, xa.data_ptr(), kd.data_ptr(), ld - 1, gd, xb.data_ptr(), Bd, stream)), Bd, steps=3)
+                del xa, xb, kd, xo
+                cd.close()
+            except Exception as ex:  # a side measurement never costs the headline line
+                secondary["ckks_n%d_error" % Pd.N] = str(ex)[:200]
         # CKKS bootstrapping N=2^16 (configs[4]): one `bootstrap` node = level 0 -> level 9 on the 25 Q + 5 P chain; random
         # residues for ciphertext and keys (the op sequence is data-independent; parity / precision: tests/test_bootstrap_gpu.py,
         # tests/test_runner_gpu.py[ckks_btp64k_bootstrap])
@@ -507,7 +529,7 @@ def run_ours(args):
             c16.close()
         except Exception as ex:  # never lose the headline line to a side measurement
             secondary["ckks_bootstrap_error"] = str(ex)[:200]
-        secondary["note"] = ("device-resident, CUDA events, batches 1024 / 256 / 64 / 8; random residues (throughput does "
+        secondary["note"] = ("device-resident, CUDA events, batches 1024 / 256 / 64 / 8 (default n=32768 / 65536 sets: 64 / 16); random residues (throughput does "
                              "not depend on values)")
 
     # multi-GPU only: the path's one exchange step -- the limb-sharded key-switch for N=2^16 through

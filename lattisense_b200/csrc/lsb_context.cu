@@ -154,25 +154,37 @@ static inline u64 ckey(int kind, int a, int b = 0, int c = 0) {
     return ((u64)kind << 56) | ((u64)(a & 0xFFFFF) << 32) | ((u64)(b & 0xFFFF) << 16) | (u64)(c & 0xFFFF);
 }
 
+// Digits of a key-switch are extended and transformed in launch groups of at most this many: a launch addresses its rows
+// through uint8_t slots (< 256) and at most kMaxRows of them.  Every parameter set up to beta * (l + k) = 192 -- all of
+// BASELINE's, cfg5's 150 included -- is one group; the reference frontend's default CKKS n = 65536 set (30 Q + 4 P
+// limbs, parameter.json) at its top levels (beta = 8, 272 extended limbs) takes two.
+int Context::ks_digit_group(int level) const {
+    const int l = level + 1, lk_ = l + np, b = beta(level);
+    int g = b;
+    while (g > 1 && (g * lk_ > 256 || g * lk_ - std::min(l, g * np) > kMaxRows)) g--;
+    return g;
+}
+
 const BexJob* Context::modup_jobs(int level, int coeff_slot0) {
     std::lock_guard<std::mutex> lk(mu_);
     const u64 key = ckey(1, level, coeff_slot0);
     auto it = cache_.find(key);
     if (it != cache_.end()) return (const BexJob*)it->second;
-    const int l = level + 1, alpha = np, b = beta(level), lk_ = l + np;
+    const int l = level + 1, alpha = np, b = beta(level), lk_ = l + np, grp = ks_digit_group(level);
     std::vector<BexJob> jobs;
     for (int d = 0; d < b; d++) {
         const int st = d * alpha, ed = std::min(st + alpha, l);
+        const int dg = d % grp;  // destination slots are relative to the digit's launch group (ks_decompose, lsb_ops.cu)
         std::vector<int> src, dst, slots;
         for (int i = st; i < ed; i++) src.push_back(i);
         for (int i = 0; i < l; i++)
             if (i < st || i >= ed) {
                 dst.push_back(i);
-                slots.push_back(d * lk_ + i);
+                slots.push_back(dg * lk_ + i);
             }
         for (int j = 0; j < np; j++) {
             dst.push_back(idxP(j));
-            slots.push_back(d * lk_ + l + j);
+            slots.push_back(dg * lk_ + l + j);
         }
         BexJob job = make_bex(src, dst);
         job.centered = (ed - st == 1) ? 1 : 0;  // rlwe DecomposeAndSplit single-modulus digit

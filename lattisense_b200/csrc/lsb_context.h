@@ -52,7 +52,8 @@ struct Context {
     size_t evk_words(int key_level) const { return (size_t)beta(key_level) * 2 * (key_level + 1 + np) * N; }
 
     // ---- cached device-side tables (built on first use; thread-safe) ----
-    const BexJob* modup_jobs(int level, int coeff_slot0);   // beta jobs
+    int ks_digit_group(int level) const;                    // digits per launch group of the key-switch ModUp (>= beta: one group)
+    const BexJob* modup_jobs(int level, int coeff_slot0);   // beta jobs; destination slots relative to the digit's group
     const BexJob* moddown_jobs(int level);                  // 2 jobs (one per polynomial)
     const FinishMap* moddown_finish(int level, int addmask, int out_stride);  // rows (p,i); addmask bit p: add c_p
     const FinishMap* rescale_finish(int level, int npoly);

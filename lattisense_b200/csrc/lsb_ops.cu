@@ -79,21 +79,28 @@ static void ks_decompose(OpEnv& e, int level, BatchPtr c_coeff, int coeff_slot0,
     Context& c = e.c;
     const DeviceTables& dt = c.dt;
     const int l = level + 1, k = c.np, lk = l + k, beta = c.beta(level), alpha = k;
-    {
-        const BexJob* jobs = c.modup_jobs(level, coeff_slot0);
-        launch_basis_extend(dt, jobs, beta, c_coeff, ext, ext, nb, e.s, c.bex_meta(jobs));
+    // digits go in launch groups whose rows fit the uint8_t slots of one launch (one group for every BASELINE configuration)
+    const int grp = c.ks_digit_group(level);
+    LSB_CHECK(grp == beta || ext.table == nullptr, "lsb: grouped key-switch digits need a strided scratch block");
+    const BexJob* jobs = c.modup_jobs(level, coeff_slot0);
+    const BexMeta* meta = c.bex_meta(jobs);
+    for (int d0 = 0; d0 < beta; d0 += grp) {
+        const int nd = std::min(grp, beta - d0);
+        BatchPtr ext_g = ext;
+        if (d0) ext_g.base += (size_t)d0 * lk * c.N;
+        launch_basis_extend(dt, jobs + d0, nd, c_coeff, ext_g, ext_g, nb, e.s, meta ? meta + d0 : nullptr);
+        RowMap m;
+        m.n = 0;
+        for (int d = d0; d < d0 + nd; d++)
+            for (int t = 0; t < lk; t++) {
+                if (t < l && t >= d * alpha && t < (d + 1) * alpha) continue;
+                LSB_CHECK(m.n < kMaxRows, "lsb: too many extended limbs");
+                m.in_slot[m.n] = m.out_slot[m.n] = (uint8_t)((d - d0) * lk + t);
+                m.mod[m.n] = (uint8_t)(t < l ? t : c.idxP(t - l));
+                m.n++;
+            }
+        launch_ntt(dt, ext_g, ext_g, m, nb, false, e.s);
     }
-    RowMap m;
-    m.n = 0;
-    for (int d = 0; d < beta; d++)
-        for (int t = 0; t < lk; t++) {
-            if (t < l && t >= d * alpha && t < (d + 1) * alpha) continue;
-            LSB_CHECK(m.n < kMaxRows, "lsb: too many extended limbs");
-            m.in_slot[m.n] = m.out_slot[m.n] = (uint8_t)(d * lk + t);
-            m.mod[m.n] = (uint8_t)(t < l ? t : c.idxP(t - l));
-            m.n++;
-        }
-    launch_ntt(dt, ext, ext, m, nb, false, e.s);
 }
 // scratch: [acc 2(l+k) | md 2l] limbs per item
 static void ks_apply(OpEnv& e, int level, BatchPtr ext, BatchPtr c_ntt, int ntt_slot0, const u64* evk, int key_level, BatchPtr addend,

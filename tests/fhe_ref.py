@@ -97,6 +97,25 @@ _BTP_P = [0x1FFFFFFFFFE00001, 0x1FFFFFFFFFC80001, 0x1FFFFFFFFFB40001, 0x1FFFFFFF
 CKKS_BTP_N16 = Params("ckks_btp_n65536", SCHEME_CKKS, 16, _BTP_Q, _BTP_P, scale=2.0 ** 40)
 CKKS_BTP_N13 = Params("ckks_btp_toy_n8192", SCHEME_CKKS, 13, _BTP_Q, _BTP_P, scale=2.0 ** 40)
 CKKS_BTP_N15 = Params("ckks_btp_n32768", SCHEME_CKKS, 15, _BTP_Q, _BTP_P, scale=2.0 ** 40)
+# the reference frontend's default CKKS sets for n = 32768 and n = 65536 (frontend/parameter.json "CKKS"/"32768", "65536";
+# the file says max_level 33 for the latter but lists 30 Q primes -- SURVEY.md fact 8 -- so the chain here has levels 0..29).
+# At its top levels the n = 65536 set has beta = 8 digits over 34 limbs = 272 extended limbs: more than one launch group
+# of the key-switch ModUp (Context::ks_digit_group).
+CKKS_N15 = Params("ckks_n32768", SCHEME_CKKS, 15,
+                  [0x4000000120001, 0x10000140001, 0xFFFFE80001, 0x10000290001, 0xFFFFC40001, 0x100003E0001, 0x10000470001,
+                   0x100004B0001, 0xFFFFB20001, 0x10000500001, 0x10000650001, 0xFFFF940001, 0xFFFF8A0001, 0xFFFF820001,
+                   0xFFFF780001, 0x10000890001, 0xFFFF750001, 0x10000960001],
+                  [0x40000001B0001, 0x3FFFFFFDF0001, 0x4000000270001], scale=2.0 ** 40)
+CKKS_N16 = Params("ckks_n65536", SCHEME_CKKS, 16,
+                  [0x80000000080001, 0x2000000A0001, 0x2000000E0001, 0x1FFFFFC20001, 0x200000440001, 0x200000500001,
+                   0x200000620001, 0x1FFFFF980001, 0x2000006A0001, 0x1FFFFF7E0001, 0x200000860001, 0x200000A60001,
+                   0x200000AA0001, 0x200000B20001, 0x200000FE0001, 0x1FFFFEDE0001, 0x1FFFFECA0001, 0x1FFFFEB40001,
+                   0x200001520001, 0x1FFFFE760001, 0x2000019A0001, 0x1FFFFE640001, 0x200001A00001, 0x1FFFFE520001,
+                   0x200001E80001, 0x1FFFFE0C0001, 0x1FFFFDEE0001, 0x200002480001, 0x1FFFFDB60001, 0x200002560001],
+                  [0x80000000440001, 0x7FFFFFFFBA0001, 0x80000000500001, 0x7FFFFFFFAA0001], scale=2.0 ** 45)
+# parity-only: 25 Q limbs with 2-limb digits (beta = 13, 351 extended limbs at the top level) on a small ring -- the
+# grouped ModUp with groups of unequal size and a short last digit
+CKKS_MANYDIGIT_N13 = Params("ckks_many_digits_n8192", SCHEME_CKKS, 13, _BTP_Q, _BTP_P[:2], scale=2.0 ** 40)
 # small-ring variants (not NTT-friendly for every reference prime, so use the n=8192 sets' primes: = 1 mod 2^14)
 CKKS_N12 = Params("ckks_small_n4096", SCHEME_CKKS, 12, CKKS_N13.q[:4], CKKS_N13.p, scale=2.0 ** 30)
 

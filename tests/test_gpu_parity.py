@@ -252,6 +252,35 @@ def test_n65536_keyswitch_parity():
             assert np.array_equal(g.rescale(want), o.rescale(want))
 
 
+@pytest.mark.parametrize("params,levels", [(R.CKKS_MANYDIGIT_N13, (24, 17, 13)), (R.CKKS_N15, (17, 8)), (R.CKKS_N16, (29, 27, 12))],
+                         ids=["many_digits_n8192", "default_n32768", "default_n65536"])
+def test_keyswitch_with_more_digits_than_one_launch_group(params, levels):
+    """Key switches whose beta * (l + k) extended limbs exceed one launch's 192 rows / 256 slots are run in digit groups
+    (Context::ks_digit_group): the reference frontend's default n = 65536 CKKS set at levels 27..29 (beta = 7..8 over 34
+    limbs), and a 2-limb-digit chain with beta = 13 on a small ring; the default n = 32768 set rides along (one group)."""
+    o, g, s = env(params)
+    rng = np.random.default_rng(211)
+    top = params.max_level
+    evk = rand_evk(o, rng, top)
+    for level in levels:
+        a, b = rand_ct(o, rng, level), rand_ct(o, rng, level)
+        ct3 = o.mult(a, b)
+        want = o.relin(ct3, evk)
+        assert np.array_equal(g.relin(ct3, evk), want), ("relin", level)
+        assert np.array_equal(g.mult_relin(a, b, evk, rescale=True), o.rescale(want)), ("mult_relin_rescale", level)
+        gal = R.galois_for_col_step(o.N, 3)
+        assert np.array_equal(g.rotate(a, evk, gal), o.rotate(a, evk, gal)), ("rotate", level)
+    if params.logN <= 13:
+        # hoisted rotations share the grouped decomposition
+        level = levels[0]
+        a = rand_ct(o, rng, level)
+        gals = [R.galois_for_col_step(o.N, st) for st in (1, 2, 5)]
+        keys = [rand_evk(o, rng, top) for _ in gals]
+        got = g.rotate_hoisted(a, keys, gals)
+        for i, gal in enumerate(gals):
+            assert np.array_equal(got[i], o.rotate(a, keys[i], gal)), ("hoisted", gal)
+
+
 def test_errors_are_reported_not_swallowed():
     import lattisense_b200 as L
     params = R.CKKS_N12

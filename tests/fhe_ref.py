@@ -113,6 +113,15 @@ CKKS_N16 = Params("ckks_n65536", SCHEME_CKKS, 16,
                    0x200001520001, 0x1FFFFE760001, 0x2000019A0001, 0x1FFFFE640001, 0x200001A00001, 0x1FFFFE520001,
                    0x200001E80001, 0x1FFFFE0C0001, 0x1FFFFDEE0001, 0x200002480001, 0x1FFFFDB60001, 0x200002560001],
                   [0x80000000440001, 0x7FFFFFFFBA0001, 0x80000000500001, 0x7FFFFFFFAA0001], scale=2.0 ** 45)
+# the remaining default sets of frontend/parameter.json (BFV 8192 / 16384 and CKKS 8192 / 16384 are BFV_N13, BFV_N14,
+# CKKS_N13, CKKS_N14 above)
+BFV_N12 = Params("bfv_n4096", SCHEME_BFV, 12, [0x7FFFFEC001, 0x8000016001], [0x40002001], t=65537)
+CKKS_N12_DEFAULT = Params("ckks_n4096", SCHEME_CKKS, 12, [0x200000E001, 0x100006001], [0x3FFFFEA001], scale=2.0 ** 32)
+BFV_N15 = Params("bfv_n32768", SCHEME_BFV, 15,
+                 [0x7FFFFFFFFE70001, 0x7FFFFFFFFE10001, 0x7FFFFFFFFCC0001, 0x400000000270001, 0x400000000350001,
+                  0x400000000360001, 0x3FFFFFFFFC10001, 0x3FFFFFFFFBE0001, 0x3FFFFFFFFBD0001, 0x4000000004D0001,
+                  0x400000000570001, 0x400000000660001],
+                 [0xFFFFFFFFFFC0001, 0x10000000001D0001, 0x10000000006E0001], t=65537)
 # parity-only: 25 Q limbs with 2-limb digits (beta = 13, 351 extended limbs at the top level) on a small ring -- the
 # grouped ModUp with groups of unequal size and a short last digit
 CKKS_MANYDIGIT_N13 = Params("ckks_many_digits_n8192", SCHEME_CKKS, 13, _BTP_Q, _BTP_P[:2], scale=2.0 ** 40)

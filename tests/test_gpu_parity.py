@@ -281,6 +281,24 @@ def test_keyswitch_with_more_digits_than_one_launch_group(params, levels):
             assert np.array_equal(got[i], o.rotate(a, keys[i], gal)), ("hoisted", gal)
 
 
+@pytest.mark.parametrize("params", [R.BFV_N12, R.CKKS_N12_DEFAULT, R.BFV_N15], ids=lambda p: p.name)
+def test_remaining_default_parameter_sets(params):
+    """frontend/parameter.json's default sets that no other test uses (n = 4096 for both schemes, BFV n = 32768 with its
+    12 Q + 3 P limbs of 58-61 bits): mult / relin / rescale / rotate at the top level and at level 1"""
+    o, g, s = env(params)
+    rng = np.random.default_rng(223)
+    top = params.max_level
+    rlk = o.gen_rlk(s, 5, top)
+    gal = R.galois_for_col_step(o.N, 2)
+    glk = o.gen_glk(s, 6, top, gal)
+    for level in sorted({top, 1}):
+        a, b = rand_ct(o, rng, level), rand_ct(o, rng, level)
+        want = o.relin(o.mult(a, b), rlk)
+        assert np.array_equal(g.mult_relin(a, b, rlk), want), ("mult_relin", level)
+        assert np.array_equal(g.rescale(want), o.rescale(want)), ("rescale", level)
+        assert np.array_equal(g.rotate(a, glk, gal), o.rotate(a, glk, gal)), ("rotate", level)
+
+
 def test_errors_are_reported_not_swallowed():
     import lattisense_b200 as L
     params = R.CKKS_N12

@@ -53,6 +53,10 @@ int lsb_stream_sync(lsb_context_t ctx, void* stream);
 /* Max batch items per scratch pass (0 = automatic, sized to keep scratch L2-resident). */
 void lsb_set_chunk(lsb_context_t ctx, int chunk);
 
+/* Streams: every operation below is enqueued on `stream` and returns without waiting.  A context owns ONE scratch block
+ * shared by all its operations; calls are serialised on the host, and when a call names another stream than the previous
+ * call on the same context it is first ordered (event wait) after the previous stream's work.  Concurrent GPU execution
+ * of two operations therefore needs two contexts. */
 /* Batched negacyclic NTT / INTT over `rows` limbs per item; limb r uses modulus index mod_idx[r % period].
  * Stands in for the HEonGPU NTT under every operator; ordering = Lattigo ring.NTT / ring.InvNTT. */
 int lsb_ntt(lsb_context_t ctx, const uint64_t* d_in, uint64_t* d_out, int rows, const int* mod_idx, int period,
@@ -67,7 +71,6 @@ int lsb_relin(lsb_context_t ctx, int level, const uint64_t* d_ct3, const uint64_
 /* bind_gpu_rescale (mega_ag_executors_gpu.cu:240-248; CPU :244-255). */
 int lsb_rescale(lsb_context_t ctx, int level, int npoly, const uint64_t* d_in, uint64_t* d_out, int batch,
                 void* stream);
-/* bind_gpu_drop_level (mega_ag_executors_gpu.cu:250-262). */
 /* CKKS ModRaise, the first step of bootstrapping (reference: CkksBtpContext::bootstrap behind
  * mega_ag_executors_gpu.cu:410-426 / mega_ag_executors_cpu.cpp:451-468; Lattigo ckks/bootstrapping): level-0
  * ciphertext [npoly][1][N] -> [npoly][top_level+1][N], the centred residues mod q_0 re-read modulo every prime. */
@@ -94,6 +97,7 @@ int lsb_mod_raise_static(lsb_context_t ctx, int top_level, int npoly, const uint
 int lsb_linear_transform(lsb_context_t ctx, int level, const uint64_t* d_ct, int n_diag, const int* diag_rot,
                          const uint64_t* const* d_diag_pt, int n1, int n_keys, const int* key_rot,
                          const uint64_t* const* d_glk, int key_level, uint64_t* d_out, void* stream);
+/* bind_gpu_drop_level (mega_ag_executors_gpu.cu:250-262). */
 int lsb_drop_level(lsb_context_t ctx, int level, int npoly, const uint64_t* d_in, uint64_t* d_out, int batch,
                    void* stream);
 /* bind_gpu_rotate_col / bind_gpu_rotate_row (mega_ag_executors_gpu.cu:264-292): automorphism X -> X^gal

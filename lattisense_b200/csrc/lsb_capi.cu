@@ -11,7 +11,33 @@ struct lsb_context_st {
     std::unique_ptr<Context> c;
     std::mutex mu;  // serialises users of the default workspace
     int chunk = 0;
+    // the default workspace is shared by every call on this context: when a call arrives on another stream than the
+    // previous one, it is ordered after the previous stream's work (which may still be using the scratch block)
+    cudaStream_t last_stream = nullptr;
+    bool has_last = false;
+    cudaEvent_t switch_ev = nullptr;
+    ~lsb_context_st() {
+        if (switch_ev && c) {
+            cudaSetDevice(c->device);
+            cudaEventDestroy(switch_ev);
+        }
+    }
 };
+
+static void order_after_previous_stream(lsb_context_st* h, cudaStream_t s) {  // h->mu held
+    if (h->has_last && h->last_stream != s) {
+        LSB_CUDA(cudaSetDevice(h->c->device));
+        if (!h->switch_ev) LSB_CUDA(cudaEventCreateWithFlags(&h->switch_ev, cudaEventDisableTiming));
+        if (cudaEventRecord(h->switch_ev, h->last_stream) == cudaSuccess) {
+            LSB_CUDA(cudaStreamWaitEvent(s, h->switch_ev, 0));
+        } else {  // the previous stream no longer exists: everything it was given has to be complete before the scratch is reused
+            cudaGetLastError();
+            LSB_CUDA(cudaDeviceSynchronize());
+        }
+    }
+    h->last_stream = s;
+    h->has_last = true;
+}
 
 static thread_local std::string g_err;
 
@@ -41,6 +67,7 @@ static int run_op(lsb_context_t h, void* stream, F&& f) {
     LSB_API_BEGIN
     LSB_CHECK(h && h->c, "lsb: null context");
     std::lock_guard<std::mutex> lk(h->mu);
+    order_after_previous_stream(h, (cudaStream_t)stream);
     OpEnv e{*h->c, h->c->default_workspace(), (cudaStream_t)stream, h->chunk};
     f(e);
     return 0;
@@ -403,6 +430,7 @@ int lsb_bootstrap_run(lsb_bootstrap_t h, const uint64_t* d_ct0, const uint64_t* 
     LSB_CHECK(h && h->b && h->ctx && h->ctx->c, "lsb: null bootstrap handle");
     Context& c = *h->ctx->c;
     std::lock_guard<std::mutex> lk(h->ctx->mu);
+    order_after_previous_stream(h->ctx, (cudaStream_t)stream);
     BootstrapKeys k;
     k.rlk = d_rlk;
     k.key_level = key_level;

@@ -299,6 +299,41 @@ def test_remaining_default_parameter_sets(params):
         assert np.array_equal(g.rotate(a, glk, gal), o.rotate(a, glk, gal)), ("rotate", level)
 
 
+def test_calls_on_two_streams_share_the_scratch_block_safely():
+    """One context, its default scratch block, two streams, no synchronisation by the caller between the calls: the
+    library orders a call after the previous stream's work when the stream changes (the scratch is still in use there),
+    so both results equal the ones of the same calls made one after the other."""
+    import torch
+    params = R.CKKS_N14
+    o, g, s = env(params)
+    rng = np.random.default_rng(227)
+    level, B = 3, 96
+    rlk = rand_evk(o, rng, level)
+    a, b = rand_ct(o, rng, level, batch=B), rand_ct(o, rng, level, batch=B)
+    c = rand_ct(o, rng, level, batch=B)
+    want_ab = g.mult_relin(a, b, rlk)
+    want_ac = g.mult_relin(a, c, rlk)
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    da, db, dc, dk = g.upload(a), g.upload(b), g.upload(c), g.upload(rlk)
+    import lattisense_b200 as L
+    o1, o2 = L.DevBuf(g, want_ab.size), L.DevBuf(g, want_ac.size)
+    keep = g.stream
+    try:
+        for _ in range(3):
+            g.stream = s1.cuda_stream
+            g.mult_relin_dev(level, da, db, dk, level, o1, B)
+            g.stream = s2.cuda_stream
+            g.mult_relin_dev(level, da, dc, dk, level, o2, B)
+        s1.synchronize()
+        s2.synchronize()
+    finally:
+        g.stream = keep
+    assert np.array_equal(g.download(o1, want_ab.shape), want_ab)
+    assert np.array_equal(g.download(o2, want_ac.shape), want_ac)
+    for d in (da, db, dc, dk, o1, o2):
+        d.free()
+
+
 def test_errors_are_reported_not_swallowed():
     import lattisense_b200 as L
     params = R.CKKS_N12

@@ -443,8 +443,75 @@ def gen_custom_start():
         emit(f"{tag}_custom_cmpac", [Argument("in_x_list", xs), Argument("in_y_list", ys)], [Argument("out_z_list", final)])
 
 
+def gen_power_mul_coeff(max_power=300, lanes=(2, 1, 2)):
+    """unittests/test_gpu_bfv.py:790-880 (BFV_power_mul_coeff): per lane a ct x pt_ringt multiply-accumulate over `max_power`
+    ciphertext powers, split into 4 partial sums above 100 terms, + a plaintext constant, rescale; the ciphertexts are shared
+    by every lane.  The reference runs it at n = 16384 with max_power 1137 (and skips it when the power-DAG files of its sister
+    test are absent); here the same generator at the n = 8192 fixture parameters with 300 powers (75-term sums)."""
+    set_fhe_param(bfv8k())
+    lv = 1
+    all_c = [[BfvCiphertextNode(f"c{k}_{i + 1}", level=lv) for i in range(max_power)] for k in range(lanes[1])]
+    all_p0, all_p, all_z = [], [], []
+    for r in range(lanes[0]):
+        p0_l, p_l, z_l = [], [], []
+        for k in range(lanes[1]):
+            p0 = [BfvPlaintextNode(f"p{r}_{k}_{i}_0", level=lv) for i in range(lanes[2])]
+            pl = [[BfvPlaintextRingtNode(f"p{r}_{k}_{i}_{j + 1}") for j in range(max_power)] for i in range(lanes[2])]
+            p0_l.append(p0)
+            p_l.append(pl)
+            z = []
+            for i in range(lanes[2]):
+                n_split, x_mac = 4, None
+                for i_split in range(n_split):
+                    a, b = int(max_power / n_split * i_split), int(max_power / n_split * (i_split + 1))
+                    x = ct_pt_mult_accumulate(all_c[k][a:b], pl[i][a:b])
+                    x_mac = x if i_split == 0 else add(x, x_mac)
+                y = add(x_mac, p0[i], f"y{r}_{k}_{i}")
+                z.append(rescale(y, f"z{r}_{k}_{i}"))
+            z_l.append(z)
+        all_p0.append(p0_l)
+        all_p.append(p_l)
+        all_z.append(z_l)
+    emit("bfv8k_power_mul_coeff", [Argument("in_c_list", all_c), Argument("in_p0_list", all_p0), Argument("in_p_list", all_p)],
+         [Argument("out_z_list", all_z)])
+
+
+def gen_euclidean_distance(n_ct=2, pack=4, skip=256, level=3):
+    """examples/ckks_euclidean_distance_cpu/ckks_euclidean_distance_cpu.py:26-70 at the default n = 16384 set: add, square +
+    relin + rescale, rotate_cols by skip, 2*skip, 3*skip (the last one two key switches through the power-of-two keys), sums,
+    a pt_ringt mask, rescale.  The example uses one ciphertext pair; two here so that the outer sum has a term."""
+    set_fhe_param(CkksParam.create_default_param(n=16384))  # the example names a constructor that no longer exists
+    xs = [CkksCiphertextNode(f"x_{i}", level=level) for i in range(n_ct)]
+    ws = [CkksCiphertextNode(f"w_{i}", level=level) for i in range(n_ct)]
+    mask = CkksPlaintextRingtNode(id="mask")
+    sums = []
+    for i in range(n_ct):
+        z = add(xs[i], ws[i], f"z_{i}")
+        u = rescale(mult_relin(z, z), f"u_{i}")
+        rots, step = [u], skip
+        for j in range(pack - 1):
+            rots.append(rotate_cols(u, step, f"u_rot_{i}_{j}")[0])
+            step += skip
+        acc = rots[0]
+        for k in range(1, len(rots)):
+            acc = add(acc, rots[k], f"sum_{i}_{k}")
+        sums.append(acc)
+    total = sums[0]
+    for i in range(1, n_ct):
+        total = add(total, sums[i], f"sum_{i}")
+    distance = rescale(mult(total, mask, "distance"))
+    emit("ckks16k_euclidean_distance", [Argument("x_input", xs), Argument("w_input_inv", ws), Argument("mask", mask)],
+         [Argument("d", distance)])
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if sys.argv[1:] == ["power"]:
+        gen_power_mul_coeff()
+        sys.exit(0)
+    if sys.argv[1:] == ["euclid"]:
+        gen_euclidean_distance()
+        sys.exit(0)
     if sys.argv[1:] == ["custom"]:
         gen_custom_start()
         sys.exit(0)

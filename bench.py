@@ -202,6 +202,148 @@ def write_cfg2_task(path, B, P):
         json.dump(sig, f)
 
 
+def write_benchmark_gpu_task(path, kind, B, P, level=3):
+    """The three graphs of the reference's own GPU benchmark (examples/benchmark_gpu/benchmark_gpu.py:26-75: 1024 x BFV
+    mult_relin, 1024 x CKKS mult_relin, 1024 x BFV rotate_cols(x, 1), all n = 16384, level 3) in the format the frontend
+    emits (compare tests/golden/graphs/cfg1_bfv_mult and bfv16k_rotate_col_l3, which the reference frontend generated)."""
+    os.makedirs(path, exist_ok=True)
+    bfv = kind.startswith("bfv")
+    ct = lambda i, deg=1, t="ct": {"id": i, "type": t, "level": level, "degree": deg, "is_ntt": not bfv, "is_mform": False,
+                                   "poly1_rns_sp_decomped": False}
+    key = lambda i, t: {"id": i, "type": t, "level": level, "degree": 1, "is_ntt": True, "is_mform": True, "sp_level": len(P.p) - 1}
+    data, comp, nd = {}, {}, 0
+    xs, ys, zs = [], [], []
+    for i in range(B):
+        data[str(nd)] = ct("x_%d" % i); xs.append(nd); nd += 1
+    if kind.endswith("mult_relin"):
+        for i in range(B):
+            data[str(nd)] = ct("y_%d" % i); ys.append(nd); nd += 1
+        k = nd
+        data[str(nd)] = key("rlk_ntt", "rlk"); nd += 1
+        for i in range(B):
+            data[str(nd)] = ct("t3_%d" % i, 2, "ct3")
+            data[str(nd + 1)] = ct("z_%d" % i)
+            comp[str(2 * i)] = {"id": "m%d" % i, "type": "mult", "inputs": [xs[i], ys[i]], "outputs": [nd]}
+            comp[str(2 * i + 1)] = {"id": "r%d" % i, "type": "relin", "inputs": [nd, k], "outputs": [nd + 1]}
+            zs.append(nd + 1)
+            nd += 2
+        keys = {"rlk": level, "glk": {}}
+        online_in = [("xs", B), ("ys", B)]
+    else:
+        k = nd
+        data[str(nd)] = dict(key("glk_ntt_col_5", "glk"), galois_element=5); nd += 1
+        for i in range(B):
+            data[str(nd)] = ct("y_%d" % i)
+            comp[str(i)] = {"id": "c%d" % i, "type": "rotate_col", "inputs": [xs[i], k], "outputs": [nd], "step": 1}
+            zs.append(nd)
+            nd += 1
+        keys = {"rlk": -1, "glk": {"5": level}}
+        online_in = [("xs", B)]
+    par = {"n": P.N, "max_level": len(P.q) - 1, "q": P.q, "p": P.p}
+    par.update({"t": P.t} if bfv else {"slots": P.N // 2, "scale": P.scale})
+    g = {"name": "Acc task", "algorithm": "BFV" if bfv else "CKKS", "data": data, "compute": comp, "inputs": xs + ys + [k],
+         "outputs": zs, "offline_inputs": [], "parameter": par}
+    sig = {"algorithm": g["algorithm"], "key": keys,
+           "online": [{"id": n, "type": "ct", "size": [c], "level": level, "phase": "in"} for n, c in online_in] +
+                     [{"id": "out", "type": "ct", "size": [B], "level": level, "phase": "out"}], "offline": []}
+    with open(os.path.join(path, "mega_ag.json"), "w") as f:
+        json.dump(g, f)
+    with open(os.path.join(path, "task_signature.json"), "w") as f:
+        json.dump(sig, f)
+
+
+def reference_benchmark_gpu(device, B=1024, level=3):
+    """examples/benchmark_gpu: wall time of one run_fhe_gpu_task call on a warm task handle (what benchmark_gpu.cpp:50 prints:
+    EXPORT + H2D + kernels + D2H + IMPORT), host limb buffers in and out, random residues for ciphertexts and keys (throughput
+    does not depend on the values; parity of these node types: tests/test_runner_gpu.py)."""
+    import ctypes as C
+    import shutil
+    import tempfile
+    import torch
+    import fhe_ref as R
+    import graph_eval as GE
+    out = {}
+    u64p = C.POINTER(C.c_uint64)
+    ia = lambda v: (C.c_int * len(v))(*v)
+
+    def limbs(lead, mods, n):
+        t = torch.empty(lead + (len(mods), n), dtype=torch.int64)
+        for i, m in enumerate(mods):
+            t[..., i, :] = torch.randint(0, m, lead + (n,), dtype=torch.int64)
+        return t
+
+    for kind, P in (("bfv_mult_relin", R.BFV_N14), ("ckks_mult_relin", R.CKKS_N14), ("bfv_rotate_col", R.BFV_N14)):
+        d = tempfile.mkdtemp(prefix="lsb_refbench_")
+        try:
+            write_benchmark_gpu_task(d, kind, B, P, level)
+            l = level + 1
+
+            def handle(ptr, k, deg=1):
+                t = GE.THandle()
+                t.kind, t.level, t.degree, t.n, t.k = k, level, deg, P.N, len(P.p)
+                t.data = C.cast(ptr, u64p)
+                return t
+
+            ct_bytes = 2 * l * P.N * 8
+            groups = [limbs((B, 2), P.q[:l], P.N)]
+            if kind.endswith("mult_relin"):
+                groups.append(limbs((B, 2), P.q[:l], P.N))
+            evk = limbs((P.beta(level), 2), P.q[:l] + P.p, P.N)
+            res = torch.empty((B, 2, l, P.N), dtype=torch.int64)
+            h_in = [handle(g.data_ptr() + i * ct_bytes, 0) for g in groups for i in range(B)]
+            keep = []
+            if kind.endswith("mult_relin"):
+                h_in.append(handle(evk.data_ptr(), 3))
+                meta_in = (ia([GE.TYPE_CIPHERTEXT] * 2 + [GE.TYPE_RELIN_KEY]), ia([level] * 3), ia([B, B, 1]))
+            else:
+                sub = handle(evk.data_ptr(), 3)
+                ga = (C.c_uint64 * 1)(5)
+                parr = (C.POINTER(GE.THandle) * 1)(C.pointer(sub))
+                hs = GE.THandle()
+                hs.kind, hs.n, hs.k, hs.n_keys = 4, P.N, len(P.p), 1
+                hs.galois_elements = C.cast(ga, u64p)
+                hs.keys = parr
+                keep += [sub, ga, parr]
+                h_in.append(hs)
+                meta_in = (ia([GE.TYPE_CIPHERTEXT, GE.TYPE_GALOIS_KEY]), ia([level, -1]), ia([B, 1]))
+            h_out = [handle(res.data_ptr() + i * ct_bytes, 0) for i in range(B)]
+            meta_out = (ia([GE.TYPE_CIPHERTEXT]), ia([level]), ia([B]))
+            in_ptrs = (C.POINTER(GE.THandle) * len(h_in))(*[C.pointer(x) for x in h_in])
+            out_ptrs = (C.POINTER(GE.THandle) * len(h_out))(*[C.pointer(x) for x in h_out])
+            prog = (C.c_int * 3)()
+            h = GE.harness()
+            task = h.th_open(d.encode(), 1)
+            if not task:
+                raise RuntimeError("th_open: " + h.th_last_error().decode())
+            try:
+                def run():
+                    rc = h.th_run(task, len(meta_in[0]), meta_in[0], meta_in[1], meta_in[2], in_ptrs, 1, meta_out[0], meta_out[1],
+                                  meta_out[2], out_ptrs, device, prog)
+                    if rc != 0:
+                        raise RuntimeError("run_fhe_gpu_task failed: " + h.th_last_error().decode())
+                res.fill_(-1)
+                run()  # warm-up: context, tables, pools, key upload
+                if bool((res == -1).any()):
+                    raise RuntimeError("the run left output limbs unwritten")
+                best = 1e30
+                for _ in range(3):
+                    t0 = time.perf_counter()
+                    run()
+                    best = min(best, time.perf_counter() - t0)
+                out[kind + "_x%d_ms" % B] = 1e3 * best
+                out[kind + "_ops_per_s"] = B / best
+            finally:
+                h.th_close(task)
+            del groups, evk, res
+        except Exception as ex:  # a side measurement never costs the headline line
+            out[kind + "_error"] = str(ex)[:200]
+        finally:
+            shutil.rmtree(d, ignore_errors=True)
+    out["note"] = ("the reference's examples/benchmark_gpu graphs (n=16384, level 3, %d ops each) through run_fhe_gpu_task, "
+                   "best of 3 wall-clock runs on a warm handle, host buffers in and out" % B)
+    return out
+
+
 class RunnerArm:
     """Drives create_/bind_/run_/release_fhe_gpu_task the way FheTaskGpu does (cxx_sdk_v2/cxx_fhe_task_gpu.cpp:69-117),
     with the test plug-in's EXPORT/IMPORT executors over host limb buffers (tests/harness/harness.cpp)."""
@@ -529,6 +671,8 @@ def run_ours(args):
             c16.close()
         except Exception as ex:  # never lose the headline line to a side measurement
             secondary["ckks_bootstrap_error"] = str(ex)[:200]
+        if not args.no_api:
+            secondary["reference_benchmark_gpu"] = reference_benchmark_gpu(local)
         secondary["note"] = ("device-resident, CUDA events, batches 1024 / 256 / 64 / 8 (default n=32768 / 65536 sets: 64 / 16); random residues (throughput does "
                              "not depend on values)")
 

@@ -100,6 +100,11 @@ Context::Context(int device_, int scheme_, int logN_, const u64* q, int nq_, con
         dt.twc_inv = (const Tw*)to_device(inv.data(), inv.size() * sizeof(Tw));
         dt.twc_fwd_d = (const TwD*)to_device(fwd_d.data(), fwd_d.size() * sizeof(TwD));
         dt.twc_inv_d = (const TwD*)to_device(inv_d.data(), inv_d.size() * sizeof(TwD));
+        std::vector<double> w(fwd_d.size());
+        for (size_t i = 0; i < w.size(); i++) w[i] = fwd_d[i].w;
+        dt.twc_fwd_w = (const double*)to_device(w.data(), w.size() * sizeof(double));
+        for (size_t i = 0; i < w.size(); i++) w[i] = inv_d[i].w;
+        dt.twc_inv_w = (const double*)to_device(w.data(), w.size() * sizeof(double));
     }
     ws0_.reset(new Workspace(device));
 }

@@ -21,6 +21,8 @@ struct DeviceTables {
     const Tw* twc_inv = nullptr;
     const TwD* twc_fwd_d = nullptr;
     const TwD* twc_inv_d = nullptr;
+    const double* twc_fwd_w = nullptr;  // the same tables, w only (ArithF64W)
+    const double* twc_inv_w = nullptr;
     const ModConst* mods = nullptr;
     Profiler* prof = nullptr;
     std::vector<uint8_t> f64_ok;  // host copy: modulus qualifies for the FP64 butterfly policy

@@ -168,6 +168,39 @@ struct ArithF64 {
     static LSB_HD u64 inv_canonical(V v, const ModCtx& m) { return canonical(v, m); }
 };
 
+// ArithF64 with 8-byte twiddles: the table holds w only and the quotient constant is formed where the twiddle is loaded,
+// wq = fl(w * fl(1/q)) -- one extra DMUL per twiddle (shared by the butterflies that use it) for half the twiddle bytes
+// through L1/L2, the unit the cluster kernel keeps busiest (l1tex 77 %, profiles/r02_ntt14_cluster_ncu.txt).  wq is within
+// 2^-52 (relative) of w/q instead of 2^-53, so for |y| < 2^51 the quotient estimate is off by at most 1 (0.5 from the
+// constant, 0.5 from rint) and |y*w mod q| <= q instead of 0.75 q: still "less than q per stage", which is what the
+// eligibility bound q*(logN+1) < 2^51 assumes; h - qf*q stays an integer below 2^50, exact in the FMA.  Outputs are
+// reduced to the canonical residue, so the limbs are identical to both other policies (tests/emul).
+struct ArithF64W : ArithF64 {
+    typedef double TW;
+    static LSB_HD double mulmod(double y, double w, const ModCtx& m) {
+        const double wq = d_mul(w, m.qinvd);
+        const double h = d_mul(y, w);
+        const double l = d_fma(y, w, -h);
+        const double qf = d_add(d_fma(y, wq, kMagic), -kMagic);
+        return d_add(d_fma(-qf, m.qd, h), l);
+    }
+    static LSB_HD void ct(V& x, V& y, TW t, const ModCtx& m) {
+        const double r = mulmod(y, t, m);
+        y = d_add(x, -r);
+        x = d_add(x, r);
+    }
+    static LSB_HD void gs(V& x, V& y, TW t, const ModCtx& m) {
+        const double s = d_add(x, y), d = d_add(x, -y);
+        y = mulmod(d, t, m);
+        x = s;
+    }
+    static LSB_HD void gs_last(V& x, V& y, TW ninv, TW w_ninv, const ModCtx& m) {
+        const double s = d_add(x, y), d = d_add(x, -y);
+        x = mulmod(s, ninv, m);
+        y = mulmod(d, w_ninv, m);
+    }
+};
+
 // LR consecutive forward stages on R = 2^LR values; tbase = twiddle index of the round's first stage for
 // this group (see lsb_ntt_core.h)
 //

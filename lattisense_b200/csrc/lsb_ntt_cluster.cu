@@ -56,6 +56,10 @@
 #ifndef LSB_CL14_MINB
 #define LSB_CL14_MINB 8
 #endif
+// FP64 policy of the cluster kernel: 1 = 8-byte twiddles (ArithF64W), 0 = (w, w/q) pairs (ArithF64)
+#ifndef LSB_F64_TW8
+#define LSB_F64_TW8 1
+#endif
 namespace cg = cooperative_groups;
 
 namespace lsb {
@@ -76,11 +80,18 @@ struct ClusterCfg {
 };
 
 constexpr int kMaxPeers = 8;
+#if LSB_F64_TW8
+typedef ArithF64W ArithF64C;
+#else
+typedef ArithF64 ArithF64C;
+#endif
+
 struct NttClArgs {
     BatchPtr in, out;
     int total_rows;
     const Tw* tw;     // [nmod][N]
     const TwD* tw_d;  // [nmod][N]
+    const double* tw_w;  // [nmod][N], w only (ArithF64W)
     const ModConst* mods;
     RowMap map;
     // fused finish epilogue (forward only): out[fm.out_slot[f]] = (fa[fm.a_slot[f]] - NTT(row)) * fm.c[f] (+ fadd[fm.add_slot[f]])
@@ -110,7 +121,8 @@ __device__ __forceinline__ void static_for_cl(F&& f) {
 
 template <class P>
 __device__ __forceinline__ const typename P::TW* tw_of(const NttClArgs& a, int mod, int N) {
-    if constexpr (std::is_same<P, ArithF64>::value) return a.tw_d + (size_t)mod * N;
+    if constexpr (std::is_same<P, ArithF64W>::value) return a.tw_w + (size_t)mod * N;
+    else if constexpr (std::is_same<P, ArithF64>::value) return a.tw_d + (size_t)mod * N;
     else return a.tw + (size_t)mod * N;
 }
 
@@ -236,7 +248,10 @@ __device__ __forceinline__ void ntt_cluster_body(const NttClArgs& a, u64* sm) {
 #pragma unroll
         for (int c = 0; c < CL; c++) peer[c] = CL > 1 ? cluster.map_shared_rank(sm, c) : sm;
         typename P::TW ninv, w_ninv;
-        if constexpr (std::is_same<P, ArithF64>::value) {
+        if constexpr (std::is_same<P, ArithF64W>::value) {
+            ninv = mc.ninv_d.w;
+            w_ninv = mc.w_ninv_d.w;
+        } else if constexpr (std::is_same<P, ArithF64>::value) {
             ninv = mc.ninv_d;
             w_ninv = mc.w_ninv_d;
         } else {
@@ -684,18 +699,18 @@ static void launch_cluster_k(K kernel, const NttClArgs& a, cudaStream_t s) {
 template <int LOGN>
 static void launch_cluster_n(const NttClArgs& a, bool inverse, bool f64, cudaStream_t s) {
     if (a.npeer > 0) {
-        if (f64) launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, true, ArithF64, false, true>, a, s);
+        if (f64) launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, true, ArithF64C, false, true>, a, s);
         else launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, true, ArithU64, false, true>, a, s);
         return;
     }
     if (a.fm) {
-        if (f64) launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, false, ArithF64, true>, a, s);
+        if (f64) launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, false, ArithF64C, true>, a, s);
         else launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, false, ArithU64, true>, a, s);
         return;
     }
     if (f64) {
-        if (inverse) launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, true, ArithF64, false>, a, s);
-        else launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, false, ArithF64, false>, a, s);
+        if (inverse) launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, true, ArithF64C, false>, a, s);
+        else launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, false, ArithF64C, false>, a, s);
     } else {
         if (inverse) launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, true, ArithU64, false>, a, s);
         else launch_cluster_k<LOGN>(k_ntt_cluster<LOGN, false, ArithU64, false>, a, s);
@@ -726,6 +741,7 @@ void launch_ntt_cluster(const DeviceTables& dt, BatchPtr in, BatchPtr out, const
         a.total_rows = batch * parts[f].n;
         a.tw = inverse ? dt.twc_inv : dt.twc_fwd;  // tail-SoA copies (host::soa_tail)
         a.tw_d = inverse ? dt.twc_inv_d : dt.twc_fwd_d;
+        a.tw_w = inverse ? dt.twc_inv_w : dt.twc_fwd_w;
         a.mods = dt.mods;
         a.map = parts[f];
         a.fm = fin ? fin->fm_dev : nullptr;

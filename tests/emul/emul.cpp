@@ -285,7 +285,8 @@ int emul_ntt_persist(int logN, u64 q, u64* data, int inverse, int f64) {
     }
 }
 
-// f64: 1 = FP64 butterfly policy (returns 2 if the prime does not qualify), 0 = 64-bit Shoup/Harvey policy
+// f64: 1 = FP64 butterfly policy with (w, w/q) twiddles, 2 = with 8-byte twiddles (both return 2 if the prime does not
+// qualify), 0 = 64-bit Shoup/Harvey policy
 int emul_ntt_cluster(int logN, u64 q, u64* data, int inverse, int f64) {
     try {
         const int N = 1 << logN;
@@ -298,7 +299,12 @@ int emul_ntt_cluster(int logN, u64 q, u64* data, int inverse, int f64) {
         soa_tail(iv.data(), logN, lrl);
         soa_tail(fd.data(), logN, lrl);
         soa_tail(ivd.data(), logN, lrl);
-        if (f64) {
+        if (f64 == 2) {  // FP64 policy with 8-byte twiddles (the device default, LSB_F64_TW8)
+            if (!mc.f64_ok) return 2;
+            std::vector<double> w(N);
+            for (int i = 0; i < N; i++) w[i] = inverse ? ivd[i].w : fd[i].w;
+            cluster_ntt<ArithF64W>(logN, w.data(), mc, mc.ninv_d.w, mc.w_ninv_d.w, data, inverse != 0);
+        } else if (f64) {
             if (!mc.f64_ok) return 2;
             cluster_ntt<ArithF64>(logN, inverse ? ivd.data() : fd.data(), mc, mc.ninv_d, mc.w_ninv_d, data, inverse != 0);
         } else {

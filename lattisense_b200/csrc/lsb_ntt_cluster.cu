@@ -56,6 +56,11 @@
 #ifndef LSB_CL14_MINB
 #define LSB_CL14_MINB 8
 #endif
+// forward transforms at N = 2^14 ask ptxas for 9 resident CTAs (56 registers): with the 8-byte twiddles the forward kernel
+// fits them without spills and gains 4 % (2.92 -> 3.03 TB/s), the inverse does not (2.71 -> 2.70), 10 loses 4 %
+#ifndef LSB_CL14_MINB_FWD
+#define LSB_CL14_MINB_FWD 9
+#endif
 // FP64 policy of the cluster kernel: 1 = 8-byte twiddles (ArithF64W), 0 = (w, w/q) pairs (ArithF64)
 #ifndef LSB_F64_TW8
 #define LSB_F64_TW8 1
@@ -77,6 +82,8 @@ struct ClusterCfg {
     // compiler 85 registers (inverse: 1365 -> 1538 GB/s on the mixed chain, 1004 -> 1098 GB/s on 61-bit primes)
     static constexpr int MINB = LOGN == 14 ? LSB_CL14_MINB : LOGN == 16 ? LSB_CL16_MINB : LSB_CL_MINB;
     static constexpr int G0 = BS / CL;      // cross-round groups per CTA
+    // f64w: the FP64 policy with 8-byte twiddles (the integer policy spills at 56 registers)
+    static constexpr int minb(bool inv, bool f64w) { return LOGN == 14 && !inv && f64w ? LSB_CL14_MINB_FWD : MINB; }
 };
 
 constexpr int kMaxPeers = 8;
@@ -281,7 +288,7 @@ __device__ __forceinline__ void ntt_cluster_body(const NttClArgs& a, u64* sm) {
 }
 
 template <int LOGN, bool INV, class P, bool FIN = false, bool PEERS = false>
-__global__ void __launch_bounds__(ClusterCfg<LOGN>::NT, ClusterCfg<LOGN>::MINB) k_ntt_cluster(const __grid_constant__ NttClArgs a) {
+__global__ void __launch_bounds__(ClusterCfg<LOGN>::NT, ClusterCfg<LOGN>::minb(INV, std::is_same<P, ArithF64W>::value)) k_ntt_cluster(const __grid_constant__ NttClArgs a) {
     extern __shared__ __align__(1024) u64 sm[];
     ntt_cluster_body<LOGN, INV, P, FIN, PEERS>(a, sm);
 }

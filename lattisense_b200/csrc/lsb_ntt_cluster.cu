@@ -58,6 +58,15 @@
 #endif
 // forward transforms at N = 2^14 ask ptxas for 9 resident CTAs (56 registers): with the 8-byte twiddles the forward kernel
 // fits them without spills and gains 4 % (2.92 -> 3.03 TB/s), the inverse does not (2.71 -> 2.70), 10 loses 4 %
+// resident CTAs asked of ptxas for the FP64 policy at N = 2^16 / 2^15 (tools/ab_f64_16.sh; measured with the 8-byte twiddles:
+// 4 / 5 / 6 -> forward 2219 / 2276 / 2169 GB/s, inverse 1870 / 1820 / 1606 GB/s at N = 2^16, 2652 / 2589 / 2113 and
+// 2314 / 2142 / 1223 at N = 2^15: the defaults stay)
+#ifndef LSB_CL16_MINB_F64
+#define LSB_CL16_MINB_F64 LSB_CL16_MINB
+#endif
+#ifndef LSB_CL15_MINB_F64
+#define LSB_CL15_MINB_F64 LSB_CL_MINB
+#endif
 #ifndef LSB_CL14_MINB_FWD
 #define LSB_CL14_MINB_FWD 9
 #endif
@@ -83,7 +92,9 @@ struct ClusterCfg {
     static constexpr int MINB = LOGN == 14 ? LSB_CL14_MINB : LOGN == 16 ? LSB_CL16_MINB : LSB_CL_MINB;
     static constexpr int G0 = BS / CL;      // cross-round groups per CTA
     // f64w: the FP64 policy with 8-byte twiddles (the integer policy spills at 56 registers)
-    static constexpr int minb(bool inv, bool f64w) { return LOGN == 14 && !inv && f64w ? LSB_CL14_MINB_FWD : MINB; }
+    static constexpr int minb(bool inv, bool f64w) {
+        return LOGN == 14 && !inv && f64w ? LSB_CL14_MINB_FWD : LOGN == 16 && f64w ? LSB_CL16_MINB_F64 : LOGN == 15 && f64w ? LSB_CL15_MINB_F64 : MINB;
+    }
 };
 
 constexpr int kMaxPeers = 8;

@@ -711,6 +711,27 @@ static void launch_cluster_k(K kernel, const NttClArgs& a, cudaStream_t s) {
     at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
+    static const bool report = [] {  // LSB_NTT_OCC=1: how many clusters of this kernel the device holds at once (stderr, once per kernel)
+        const char* e = getenv("LSB_NTT_OCC");
+        return e && atoi(e) != 0;
+    }();
+    if (report) {
+        static std::mutex mu;
+        static std::map<const void*, int> seen;
+        std::lock_guard<std::mutex> lk(mu);
+        if (!seen.count((const void*)kernel)) {
+            int ncl = 0, per_sm = 0, dev = 0, sms = 0;
+            cudaFuncAttributes fa;
+            cudaOccupancyMaxActiveClusters(&ncl, kernel, &cfg);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, C::NT, smem);
+            cudaFuncGetAttributes(&fa, kernel);
+            cudaGetDevice(&dev);
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            seen[(const void*)kernel] = ncl;
+            fprintf(stderr, "lsb ntt occupancy: logN %d cluster %d x %d threads, %d KiB, %d registers: %d clusters = %.2f CTAs per SM co-resident "
+                            "(%d per SM without the cluster constraint)\n", LOGN, C::CL, C::NT, smem >> 10, fa.numRegs, ncl, (double)ncl * C::CL / sms, per_sm);
+        }
+    }
     LSB_CUDA(cudaLaunchKernelEx(&cfg, kernel, a));
 }
 

@@ -106,6 +106,9 @@ Context::Context(int device_, int scheme_, int logN_, const u64* q, int nq_, con
         for (size_t i = 0; i < w.size(); i++) w[i] = inv_d[i].w;
         dt.twc_inv_w = (const double*)to_device(w.data(), w.size() * sizeof(double));
     }
+    LSB_CUDA(cudaStreamCreateWithFlags(&dt.ntt_side, cudaStreamNonBlocking));
+    LSB_CUDA(cudaEventCreateWithFlags(&dt.ntt_fork, cudaEventDisableTiming));
+    LSB_CUDA(cudaEventCreateWithFlags(&dt.ntt_join, cudaEventDisableTiming));
     ws0_.reset(new Workspace(device));
 }
 
@@ -127,6 +130,12 @@ Context::~Context() {
         cudaStreamDestroy(side_.stream);
         cudaEventDestroy(side_.fork);
         cudaEventDestroy(side_.join);
+    }
+    if (dt.ntt_side) {
+        cudaStreamSynchronize(dt.ntt_side);
+        cudaStreamDestroy(dt.ntt_side);
+        cudaEventDestroy(dt.ntt_fork);
+        cudaEventDestroy(dt.ntt_join);
     }
     ws0_.reset();
     for (void* p : owned_) cudaFree(p);

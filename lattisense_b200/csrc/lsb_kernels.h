@@ -26,6 +26,10 @@ struct DeviceTables {
     const ModConst* mods = nullptr;
     Profiler* prof = nullptr;
     std::vector<uint8_t> f64_ok;  // host copy: modulus qualifies for the FP64 butterfly policy
+    // side stream + events on which the FP64-policy rows of a mixed transform run beside the integer-policy rows
+    // (launch_ntt_cluster); owned by the Context
+    cudaStream_t ntt_side = nullptr;
+    cudaEvent_t ntt_fork = nullptr, ntt_join = nullptr;
 };
 
 // ---- NTT ----

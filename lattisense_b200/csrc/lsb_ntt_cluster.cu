@@ -758,7 +758,7 @@ static void launch_cluster_n(const NttClArgs& a, bool inverse, bool f64, cudaStr
 
 // Rows whose prime qualifies for the FP64 policy and the others go in separate launches (CTA-uniform code).
 void launch_ntt_cluster(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap& map, int batch, bool inverse,
-                        const std::vector<uint8_t>& f64_ok, bool allow_f64, cudaStream_t s, const NttFinish* fin,
+                        const std::vector<uint8_t>& f64_ok, bool allow_f64, cudaStream_t s0, const NttFinish* fin,
                         u64* const* peers, int npeer) {
     LSB_CHECK(!(fin && inverse), "lsb: the finish epilogue belongs to the forward transform");
     LSB_CHECK(npeer == 0 || (inverse && !fin && batch == 1 && npeer <= kMaxPeers && peers),
@@ -772,8 +772,21 @@ void launch_ntt_cluster(const DeviceTables& dt, BatchPtr in, BatchPtr out, const
         p.mod[p.n] = map.mod[r];
         p.n++;
     }
+    // A transform over limbs of both policies is two launches on disjoint rows: the FP64-policy one goes to a side stream so
+    // that the two share the SMs (one is bound by the FP64 pipe, the other by the integer multiplier) and neither leaves
+    // the machine half empty at its tail.  LSB_NTT_MIXED_OVERLAP=0: one after the other on `s0`.
+    static const bool overlap = [] {
+        const char* e = getenv("LSB_NTT_MIXED_OVERLAP");
+        return !(e && atoi(e) == 0);
+    }();
+    const bool two = overlap && parts[0].n > 0 && parts[1].n > 0 && npeer == 0 && dt.ntt_side != nullptr;
+    if (two) {
+        LSB_CUDA(cudaEventRecord(dt.ntt_fork, s0));
+        LSB_CUDA(cudaStreamWaitEvent(dt.ntt_side, dt.ntt_fork, 0));
+    }
     for (int f = 0; f < 2; f++) {
         if (parts[f].n == 0) continue;
+        cudaStream_t s = (two && f == 1) ? dt.ntt_side : s0;
         NttClArgs a;
         a.in = in;
         a.out = out;
@@ -819,6 +832,10 @@ void launch_ntt_cluster(const DeviceTables& dt, BatchPtr in, BatchPtr out, const
             case 16: launch_cluster_n<16>(a, inverse, f == 1, s); break;
             default: throw std::runtime_error("lsb: unsupported ring degree (logN must be 12..16)");
         }
+    }
+    if (two) {
+        LSB_CUDA(cudaEventRecord(dt.ntt_join, dt.ntt_side));
+        LSB_CUDA(cudaStreamWaitEvent(s0, dt.ntt_join, 0));
     }
 }
 

@@ -59,8 +59,39 @@ LSB_HD void bex_coeff(const BexJob& job, const ModConst* mods, const u64* x, Oth
         vf += (double)y[i] / job.s_f64[i];
     }
     const int v = (int)(u64)vf;
+    double yl[kBexMaxSrc], yh[kBexMaxSrc];
+    if (job.n_f64 > 0) {
+        for (int i = 0; i < job.ns; i++) {
+            if (job.src_split) {
+                yl[i] = f64_from_u64(y[i] & 0xFFFFFFFFull);
+                yh[i] = f64_from_u64(y[i] >> 32);
+            } else {
+                yl[i] = f64_from_u64(y[i]);
+            }
+        }
+    }
     for (int t = 0; t < job.nt; t++) {
         const ModConst& m = mods[job.dst_mod[t]];
+        if (job.t_f64[t]) {
+            // this target on the FP64 pipe (mixed-pipe CRT, lsb_tables.h bex_choose_mixed): the same sum of y_i * (S/s_i mod p),
+            // each product reduced to [-0.75 p, 0.75 p], the result brought to the canonical residue -- identical limbs
+            double acc = 0.0;
+            for (int i = 0; i < job.ns; i++) {
+                acc = d_add(acc, f64_mulmod(yl[i], job.qhat_mod_d[t][i], m.qd));
+                if (job.src_split) acc = d_add(acc, f64_mulmod(yh[i], job.qhat_mod_hi_d[t][i], m.qd));
+            }
+            acc = d_add(acc, -f64_from_u64(job.vS[t][v]));
+            if (job.mode == BEX_OTHER_SUB) {
+                const double e = f64_canon_d(acc, m.qd, m.qinvd);
+                const double d = d_add(f64_from_u64(other(t)), -e);
+                acc = d_add(f64_mulmod(d, job.mulc_d[t], m.qd), f64_from_u64(job.addc[t]));
+            } else if (job.mode == BEX_SUB_MUL) {
+                const double e = f64_canon_d(acc, m.qd, m.qinvd);
+                acc = f64_mulmod(d_add(e, -f64_from_u64(job.addc[t])), job.mulc_d[t], m.qd);
+            }
+            store(t, f64_canon_u(acc, m.qd, m.qinvd));
+            continue;
+        }
         Acc128 acc{0, 0};
         for (int i = 0; i < job.ns; i++) acc_mad(acc, y[i], job.qhat_mod[t][i]);
         u64 e = job.wide_ok ? reduce_wide(acc.lo, acc.hi, m.bq) : barrett128(acc.lo, acc.hi, m.bq);

@@ -71,6 +71,13 @@ struct BexJob {
     TwD qhat_inv_d[kBexMaxSrc];
     TwD qhat_mod_d[kBexMaxDst][kBexMaxSrc];
     TwD mulc_d[kBexMaxDst];
+    // Mixed-pipe CRT (integer path, !f64_ok): targets flagged in t_f64 (modulus below 2^47) are summed on the FP64 pipe while
+    // the others use the 64-bit integer multiplier, so that both multiply pipes of an SM work on one job.  qhat_mod_d[t] /
+    // mulc_d[t] are then valid for the flagged targets; when a source modulus reaches 2^51 (src_split) y_i enters as
+    // y_hi * 2^32 + y_lo and qhat_mod_hi_d[t][i] holds (qhat_mod[t][i] * 2^32 mod p_t).
+    int n_f64, src_split;
+    uint8_t t_f64[kBexMaxDst];
+    TwD qhat_mod_hi_d[kBexMaxDst][kBexMaxSrc];
 };
 // jobs: device array of njobs BexJob; src/dst/other: per-batch-item blocks.
 // meta: host-side description of the jobs (selects the specialised kernels); nullptr: generic kernel

@@ -62,12 +62,68 @@ inline void soa_tail(T* table, int logN, int lrl) {
     }
 }
 
+// Mixed-pipe CRT of a job that cannot run on the FP64 pipe as a whole (a source or a target modulus >= 2^47): choose which
+// of the eligible targets (modulus < 2^47, sum of the job's terms below 2^51) go to the FP64 pipe so that the two pipes
+// finish together.  Per-thread cost model from the micro-benchmarks (profiles/r01_int_pipe_microbench.txt): a 64x64->128
+// multiply-accumulate 0.22 clk/SM-lane, a reduction 0.35; an FP64-pipe instruction 1/57.8, 6 per product.
+inline void bex_choose_mixed(BexJob& j, const std::vector<u64>& moduli) {
+    using namespace host;
+    j.n_f64 = 0;
+    j.src_split = 0;
+    std::memset(j.t_f64, 0, sizeof(j.t_f64));
+    static const double bias = [] {  // LSB_BEX_MIXED=0: integer pipe only; LSB_BEX_F64_BIAS=x: scale the FP64 cost
+        const char* off = getenv("LSB_BEX_MIXED");
+        if (off && atoi(off) == 0) return -1.0;
+        const char* b = getenv("LSB_BEX_F64_BIAS");
+        return b ? atof(b) : 1.0;
+    }();
+    if (bias <= 0.0 || j.f64_ok || j.ns < 1) return;
+    for (int i = 0; i < j.ns; i++)
+        if (moduli[j.src_mod[i]] >= (1ull << 51)) j.src_split = 1;
+    const int terms = j.ns * (j.src_split ? 2 : 1);
+    std::vector<int> elig;
+    for (int t = 0; t < j.nt; t++) {
+        const u64 p = moduli[j.dst_mod[t]];
+        // |sum| <= 0.75 p * terms, then - vS (< p), then the mode's arithmetic: keep everything below 2^51
+        if (p < kElemF64Limit && (u128)p * (u128)(terms + 2) < ((u128)1 << 51)) elig.push_back(t);
+    }
+    const double cf = bias * (terms * 6.0 + 10.0) / 57.8, ci = j.ns * 0.22 + 0.35;
+    int best = 0;
+    double best_cost = j.nt * ci;
+    for (int nf = 1; nf <= (int)elig.size(); nf++) {
+        const double c = std::max(nf * cf, (j.nt - nf) * ci);
+        if (c < best_cost) {
+            best_cost = c;
+            best = nf;
+        }
+    }
+    // spread the FP64 targets over the job so that consecutive targets alternate pipes
+    for (int n = 0; n < best; n++) {
+        const int t = elig[(size_t)n * elig.size() / best];
+        j.t_f64[t] = 1;
+    }
+    j.n_f64 = best;
+    for (int t = 0; t < j.nt; t++) {
+        if (!j.t_f64[t]) continue;
+        const u64 p = moduli[j.dst_mod[t]];
+        for (int i = 0; i < j.ns; i++) {
+            j.qhat_mod_d[t][i] = make_twd(j.qhat_mod[t][i], p);
+            j.qhat_mod_hi_d[t][i] = make_twd(mulmod(j.qhat_mod[t][i], (1ull << 32) % p, p), p);
+        }
+        j.mulc_d[t] = make_twd(j.mulc[t].w, p);
+    }
+}
+
 // FP64 copies of a job's constants (call again after changing mulc): valid when every modulus is below 2^47
 inline void bex_fill_f64(BexJob& j, const std::vector<u64>& moduli) {
     j.f64_ok = 1;
     for (int i = 0; i < j.ns; i++) j.f64_ok &= moduli[j.src_mod[i]] < kElemF64Limit ? 1 : 0;
     for (int t = 0; t < j.nt; t++) j.f64_ok &= moduli[j.dst_mod[t]] < kElemF64Limit ? 1 : 0;
-    if (!j.f64_ok) return;
+    if (!j.f64_ok) {
+        bex_choose_mixed(j, moduli);  // the job stays on the integer path; some of its targets may still use the FP64 pipe
+        return;
+    }
+    j.n_f64 = 0;
     for (int i = 0; i < j.ns; i++) j.qhat_inv_d[i] = make_twd(j.qhat_inv[i].w, moduli[j.src_mod[i]]);
     for (int t = 0; t < j.nt; t++) {
         const u64 p = moduli[j.dst_mod[t]];

@@ -32,6 +32,7 @@ def emul():
     lib.emul_ntt_cluster.argtypes = [C.c_int, C.c_uint64, u64p, C.c_int, C.c_int]
     lib.emul_ntt_persist.argtypes = [C.c_int, C.c_uint64, u64p, C.c_int, C.c_int]
     lib.emul_basis_extend.argtypes = [C.c_int, u64p, C.c_int, i32p, C.c_int, i32p, C.c_int, C.c_int, u64p, u64p]
+    lib.emul_bex_mixed_targets.argtypes = [u64p, C.c_int, i32p, C.c_int, i32p, C.c_int]
     lib.emul_reduce_wide.restype = C.c_uint64
     lib.emul_reduce_wide.argtypes = [C.c_uint64] * 3
     for n in ("emul_mulmod", "emul_barrett64", "emul_mul_shoup"):

@@ -367,6 +367,14 @@ int emul_basis_extend(int logN, const u64* moduli, int nmod, const int* src, int
     }
 }
 
+// how many targets of this job the mixed-pipe CRT sends to the FP64 pipe (low byte), whether the sources are split (bit 8),
+// whether the whole job runs on the FP64 pipe (bit 9)
+int emul_bex_mixed_targets(const u64* moduli, int nmod, const int* src, int ns, const int* dst, int nt) {
+    std::vector<u64> mods(moduli, moduli + nmod);
+    BexJob job = make_bex_tables(mods, std::vector<int>(src, src + ns), std::vector<int>(dst, dst + nt));
+    return job.n_f64 | (job.src_split << 8) | (job.f64_ok << 9);
+}
+
 // a*b mod q through the device Barrett path, and 128-bit accumulate path
 u64 emul_mulmod(u64 a, u64 b, u64 q) { return mulmod(a, b, host::make_barrett(q)); }
 u64 emul_reduce_wide(u64 lo, u64 hi, u64 q) { return reduce_wide(lo, hi, host::make_barrett(q)); }

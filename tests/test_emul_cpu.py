@@ -52,8 +52,10 @@ def test_ntt_thread_count_independent(emul):
         assert np.array_equal(x, outs[0])
 
 
-@pytest.mark.parametrize("params", [R.CKKS_N13, R.BFV_N14, R.CKKS_BTP_N13], ids=lambda p: p.name)
+@pytest.mark.parametrize("params", [R.CKKS_N13, R.BFV_N14, R.CKKS_BTP_N13, R.CKKS_N16], ids=lambda p: p.name)
 def test_basis_extend_matches_oracle(emul, params):
+    """incl. the mixed-pipe CRT (lsb_tables.h bex_choose_mixed): the bootstrap chain's 60/61-bit sources enter the FP64 targets
+    as two 32-bit halves, the default n = 65536 set's 46-bit sources whole; worst-case residues ride along"""
     rng = np.random.default_rng(11)
     o = R.Oracle(params)
     mods = np.array(o.moduli, dtype=np.uint64)
@@ -68,6 +70,9 @@ def test_basis_extend_matches_oracle(emul, params):
     for src, dst, centered in combos:
         src, dst = src[:16], dst[:48]
         x = np.stack([rng.integers(0, o.moduli[i], size=params.N, dtype=np.uint64) for i in src])
+        for i, sm in enumerate(src):  # extreme residues in the first columns
+            x[i, :6] = [o.moduli[sm] - 1, 0, 1, o.moduli[sm] - 1, o.moduli[sm] // 2, min((1 << 32) - 1, o.moduli[sm] - 1)]
+        x[0, 3] = 0
         if not centered:
             want = o.basis_extend(src, x, dst)
         else:
@@ -80,6 +85,10 @@ def test_basis_extend_matches_oracle(emul, params):
                                    dtype=np.uint64)
         sa = (C.c_int * len(src))(*src)
         da = (C.c_int * len(dst))(*dst)
+        if not centered and params in (R.CKKS_BTP_N13, R.CKKS_N16):
+            mixed = emul.emul_bex_mixed_targets(R.P(mods), len(mods), sa, len(src), da, len(dst))
+            assert (mixed & 0xFF) > 0 and not (mixed >> 9), (src, dst, mixed)  # these jobs do use both pipes
+            assert bool(mixed & 0x100) == (max(o.moduli[i] for i in src) >= 2 ** 51)
         for force_int in (0, 2):  # default policy (FP64 CRT when every prime is below 2^47), then the integer CRT
             got = np.zeros((len(dst), params.N), dtype=np.uint64)
             assert emul.emul_basis_extend(params.logN, R.P(mods), len(mods), sa, len(src), da, len(dst), centered | force_int,

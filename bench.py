@@ -687,6 +687,9 @@ def run_ours(args):
             limb = KS.measure(16, 24, 16, 10, check=True, rk=Ranks())
         except Exception as ex:
             limb = {"error": str(ex)[:300]}
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
     if rank != 0:
         return
     cores = len(os.sched_getaffinity(0))

@@ -330,8 +330,23 @@ void launch_ntt(const DeviceTables& dt, BatchPtr in, BatchPtr out, const RowMap&
                 p.mod[p.n] = map.mod[r];
                 p.n++;
             }
-            if (cl.n) launch_ntt_cluster(dt, in, out, cl, batch, false, dt.f64_ok, allow_f64, s);
+            // both kinds of rows: the FP64-policy launch goes to the side stream beside the integer-policy one (as in
+            // launch_ntt_cluster; LSB_NTT_MIXED_OVERLAP=0 keeps them one after the other)
+            static const bool overlap = [] {
+                const char* e = getenv("LSB_NTT_MIXED_OVERLAP");
+                return !(e && atoi(e) == 0);
+            }();
+            const bool two = overlap && cl.n > 0 && sg.n > 0 && dt.ntt_side != nullptr;
+            if (two) {
+                LSB_CUDA(cudaEventRecord(dt.ntt_fork, s));
+                LSB_CUDA(cudaStreamWaitEvent(dt.ntt_side, dt.ntt_fork, 0));
+            }
+            if (cl.n) launch_ntt_cluster(dt, in, out, cl, batch, false, dt.f64_ok, allow_f64, two ? dt.ntt_side : s);
             if (sg.n) launch_ntt_first_round(dt, in, out, sg, batch, false, s);
+            if (two) {
+                LSB_CUDA(cudaEventRecord(dt.ntt_join, dt.ntt_side));
+                LSB_CUDA(cudaStreamWaitEvent(s, dt.ntt_join, 0));
+            }
             return;
         }
         launch_ntt_cluster(dt, in, out, map, batch, inverse, dt.f64_ok, allow_f64, s);

@@ -53,12 +53,27 @@ LSB_HD void bex_coeff(const BexJob& job, const ModConst* mods, const u64* x, Oth
         return;
     }
     u64 y[kBexMaxSrc];
-    double vf = 0.0;
+    // Overflow count = floor of Lattigo's float64 sum v = (..(y_0/s_0) + y_1/s_1 ..), divisions in limb order.  A double
+    // division is ~25 instructions, so the sum is first formed with multiplications by 1/s_i: each term is below 1 and the two
+    // sums differ by less than ns * 2^-51, hence have the same floor unless the fast one lies within 2^-40 of an integer;
+    // only then (probability ~2^-39 per coefficient) is the exact sequence run (the same scheme as k_bex_f64).
+    double yd[kBexMaxSrc];
+    double vm = 0.0;
     for (int i = 0; i < job.ns; i++) {
         y[i] = mul_shoup(x[i], job.qhat_inv[i], mods[job.src_mod[i]].q);
-        vf += (double)y[i] / job.s_f64[i];
+        yd[i] = (double)y[i];
+        vm = d_fma(yd[i], job.rs_f64[i], vm);
     }
-    const int v = (int)(u64)vf;
+    int v = (int)vm;
+    {
+        const double eps = 9.094947017729282e-13;  // 2^-40
+        const double fr = vm - (double)v;
+        if (fr < eps || fr > 1.0 - eps) {
+            double vf = 0.0;
+            for (int i = 0; i < job.ns; i++) vf += yd[i] / job.s_f64[i];
+            v = (int)(u64)vf;
+        }
+    }
     double yl[kBexMaxSrc], yh[kBexMaxSrc];
     if (job.n_f64 > 0) {
         for (int i = 0; i < job.ns; i++) {

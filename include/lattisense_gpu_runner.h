@@ -19,6 +19,7 @@
  */
 #ifndef LATTISENSE_GPU_RUNNER_H
 #define LATTISENSE_GPU_RUNNER_H
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus

@@ -71,3 +71,14 @@ int main(int argc, char** argv) {
     out = subprocess.run([exe, os.path.join(ROOT, "tests", "golden", "graphs", "ckks8k_custom_in_middle", "mega_ag.json")],
                          capture_output=True, text=True, check=True).stdout.split()
     assert int(out[1]) == 1 and int(out[2]) == 3 and int(out[0]) >= 10
+
+
+@pytest.mark.parametrize("header", ["lsb200.h", "lattisense_gpu_runner.h"])
+def test_c_abi_headers_compile_as_c_and_as_cxx(header):
+    """the two extern "C" headers are what a cgo / JNI / ctypes binding includes: plain C99 on their own, no other include
+    needed before them, and valid C++17"""
+    path = os.path.join(ROOT, "include", header)
+    for cmd in (["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-x", "c", path],
+                ["g++", "-std=c++17", "-Wall", "-Werror", "-fsyntax-only", "-x", "c++", path]):
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr[-2000:]

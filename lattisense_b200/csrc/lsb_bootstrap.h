@@ -352,8 +352,8 @@ public:
             for (size_t i = 0; i < mats.size(); i++)
                 for (const auto& kd : mats[i]) {
                     const int k = kd.first, n1 = n1s[i];
-                    if (k % n1) out.insert(k % n1);
-                    if ((k / n1) * n1) out.insert((k / n1) * n1);
+                    if (k % n1 != 0) out.insert(k % n1);
+                    if (k / n1 != 0) out.insert((k / n1) * n1);
                 }
         };
         collect(cts_mats, cts_n1);

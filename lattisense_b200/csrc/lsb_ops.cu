@@ -474,8 +474,9 @@ void op_drop_level(OpEnv& e, int level, int npoly, BatchPtr in, BatchPtr out, in
 // rotate (automorphism + key-switch)
 // ---------------------------------------------------------------------------------------------
 static int rotate_scratch_limbs(const Context& c, int level) { return 3 * (level + 1) + ks_scratch_limbs(c, level); }
+static int dual_stream_min_batch();
 static void rotate_impl(OpEnv& e, int level, BatchPtr ct, const u64* glk, int key_level, u64 gal, BatchPtr out,
-                        u64* scratch, size_t item_words, int nb) {
+                        u64* scratch, size_t item_words, int nb, cudaEvent_t after_first = nullptr) {
     Context& c = e.c;
     const DeviceTables& dt = c.dt;
     const int l = level + 1;
@@ -486,6 +487,7 @@ static void rotate_impl(OpEnv& e, int level, BatchPtr ct, const u64* glk, int ke
     if (c.scheme == SCHEME_CKKS) {
         // ckks evaluator permuteNTT: key-switch c1, add c0, permute both (oracle/orc_core.hpp:402-414)
         launch_ntt(dt, ct, c1x, rowmap_seq(l, l, 0, 0, l), nb, true, e.s);
+        if (after_first) LSB_CUDA(cudaEventRecord(after_first, e.s));
         ks_core(e, level, c1x, 0, ct, l, glk, key_level, ct, 1, tmp, l, ks_scratch, item_words, nb);
         launch_permute_ntt(dt, tmp, out, rowmap_seq(2 * l, 0, 0, 0, l), c.permute_index(gal), nb, e.s);
     } else {
@@ -500,6 +502,23 @@ void op_rotate(OpEnv& e, int level, BatchPtr ct, const u64* glk, int key_level, 
     LSB_CUDA(cudaSetDevice(e.c.device));
     const size_t item = (size_t)rotate_scratch_limbs(e.c, level) * e.c.N;
     const int l = level + 1;
+    Context& c = e.c;
+    const bool profiling = c.dt.prof && c.dt.prof->enabled.load(std::memory_order_relaxed);
+    if (c.scheme == SCHEME_CKKS && e.chunk <= 0 && batch >= dual_stream_min_batch() && !profiling &&
+        item * (size_t)batch <= scratch_budget_words()) {
+        // large CKKS batches: two half-batches on two streams, one kernel apart, as in mult_relin_chain -- the FP64-bound
+        // transforms of one half run beside the HBM-bound inner product / permutation of the other
+        const int h0 = (batch + 1) / 2, h1 = batch - h0;
+        u64* scratch = e.ws.reserve(item * batch, e.s);
+        Context::SidePipe& sp = c.side_pipe();
+        OpEnv side{e.c, e.ws, sp.stream, e.chunk};
+        rotate_impl(e, level, ct, glk, key_level, gal, out, scratch, item, h0, sp.fork);
+        LSB_CUDA(cudaStreamWaitEvent(sp.stream, sp.fork, 0));
+        rotate_impl(side, level, adv(ct, h0), glk, key_level, gal, adv(out, h0), scratch + item * h0, item, h1);
+        LSB_CUDA(cudaEventRecord(sp.join, sp.stream));
+        LSB_CUDA(cudaStreamWaitEvent(e.s, sp.join, 0));
+        return;
+    }
     const int chunk = pick_chunk(e, item, batch, e.c.beta(level) * (l + e.c.np) - l);
     u64* scratch = e.ws.reserve(item * chunk, e.s);
     for (int b0 = 0; b0 < batch; b0 += chunk) {

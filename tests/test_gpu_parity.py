@@ -334,6 +334,23 @@ def test_calls_on_two_streams_share_the_scratch_block_safely():
         d.free()
 
 
+def test_large_batches_split_over_two_streams_match_the_oracle():
+    """batches of 256 and more run as two half-batches on two streams (mult_relin chain and rotate, LSB_DUAL_STREAM): items
+    on both sides of the split, the first and the last equal the oracle's"""
+    params = R.CKKS_N13
+    o, g, s = env(params)
+    rng = np.random.default_rng(229)
+    level, B = 3, 301
+    rlk = rand_evk(o, rng, level)
+    gal = R.galois_for_col_step(o.N, 7)
+    a, b = rand_ct(o, rng, level, batch=B), rand_ct(o, rng, level, batch=B)
+    rot = g.rotate(a, rlk, gal)
+    mrr = g.mult_relin(a, b, rlk, rescale=True)
+    for i in (0, 150, 151, B - 1):
+        assert np.array_equal(rot[i], o.rotate(a[i], rlk, gal)), ("rotate", i)
+        assert np.array_equal(mrr[i], o.rescale(o.relin(o.mult(a[i], b[i]), rlk))), ("mult_relin_rescale", i)
+
+
 def test_errors_are_reported_not_swallowed():
     import lattisense_b200 as L
     params = R.CKKS_N12

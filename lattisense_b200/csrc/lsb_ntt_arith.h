@@ -229,12 +229,14 @@ LSB_HD void fwd_stages(typename P::V (&x)[1 << LR], const typename P::TW* __rest
     }
 }
 // the same stages inverted (Gentleman-Sande, last stage first).  FINAL: the round contains global stage 0.
-template <class P, int LR, bool FINAL, int S1 = -1>
+// RHI / RLO: only the stages r = RHI .. RLO of the round (the whole round by default) -- the cluster kernel's inverse cross
+// round runs its first stage, signals the cluster barrier, then runs the rest
+template <class P, int LR, bool FINAL, int S1 = -1, int RHI = LR - 1, int RLO = 0>
 LSB_HD void inv_stages(typename P::V (&x)[1 << LR], const typename P::TW* __restrict__ tw, u32 tbase, const ModCtx& m,
                        typename P::TW ninv, typename P::TW w_ninv) {
     constexpr int R = 1 << LR;
 #pragma unroll
-    for (int r = LR - 1; r >= 0; r--) {
+    for (int r = RHI; r >= RLO; r--) {
         const int hk = R >> (r + 1);
         if (FINAL && r == 0) {
 #pragma unroll
@@ -248,7 +250,7 @@ LSB_HD void inv_stages(typename P::V (&x)[1 << LR], const typename P::TW* __rest
             }
         }
     }
-    if (!FINAL) {
+    if (!FINAL && RLO == 0) {
 #pragma unroll
         for (int k = 0; k < R; k++) P::end_of_inverse_round(x[k], m);
     }

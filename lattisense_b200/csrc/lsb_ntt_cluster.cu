@@ -144,6 +144,15 @@ __device__ __forceinline__ const typename P::TW* tw_of(const NttClArgs& a, int m
     else return a.tw + (size_t)mod * N;
 }
 
+// Inverse transform: the trailing cluster barrier ("nobody reads my tile any more") is split -- a thread arrives as soon as the
+// first stage of its cross round has consumed every word it loaded from the peers' tiles (so the loads have completed), and
+// waits only after the remaining stages and the global stores.  0: one cluster.sync() at the end.
+#ifndef LSB_INV_SPLIT_BARRIER
+#define LSB_INV_SPLIT_BARRIER 1
+#endif
+__device__ __forceinline__ void cl_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cl_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+
 template <int LOGN, bool INV, class P, bool FIN, bool PEERS = false>
 __device__ __forceinline__ void ntt_cluster_body(const NttClArgs& a, u64* sm) {
     typedef ClusterCfg<LOGN> C;
@@ -276,12 +285,20 @@ __device__ __forceinline__ void ntt_cluster_body(const NttClArgs& a, u64* sm) {
             ninv = mc.ninv;
             w_ninv = mc.w_ninv;
         }
+        // (every thread runs the loop body exactly once when G0 == NT, so the barrier instructions inside it are convergent)
+        constexpr bool SPLIT = LSB_INV_SPLIT_BARRIER && CL > 1 && C::G0 == NT;
         for (int gl = tid; gl < C::G0; gl += NT) {
             const int g = rank * C::G0 + gl;
             typename P::V x[16];
 #pragma unroll
             for (int k = 0; k < 16; k++) x[k] = P::from_bits(peer[k / NB][(k % NB) * BS + swz(g)]);
-            inv_stages<P, 4, true>(x, tw, 1u, m, ninv, w_ninv);
+            if constexpr (SPLIT) {
+                inv_stages<P, 4, true, -1, 3, 3>(x, tw, 1u, m, ninv, w_ninv);  // 8 butterflies over all 16 loaded words
+                cl_arrive_relaxed();
+                inv_stages<P, 4, true, -1, 2, 0>(x, tw, 1u, m, ninv, w_ninv);
+            } else {
+                inv_stages<P, 4, true>(x, tw, 1u, m, ninv, w_ninv);
+            }
             if constexpr (!PEERS) {
 #pragma unroll
                 for (int k = 0; k < 16; k++) dst[g + k * BS] = P::inv_canonical(x[k], m);
@@ -294,7 +311,8 @@ __device__ __forceinline__ void ntt_cluster_body(const NttClArgs& a, u64* sm) {
                 }
             }
         }
-        if (CL > 1) cluster.sync();  // peers may still be reading this CTA's shared memory
+        if constexpr (SPLIT) cl_wait();  // every thread of the cluster has arrived: nobody reads this CTA's tile any more
+        else if (CL > 1) cluster.sync();  // peers may still be reading this CTA's shared memory
     }
 }
 

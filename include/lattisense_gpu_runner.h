@@ -150,6 +150,14 @@ void lsb_gpu_task_invalidate_keys(fhe_task_handle handle);
 void lsb_gpu_task_transfer_stats(fhe_task_handle handle, long long* h2d_bytes, long long* d2h_bytes, long long* zero_copy_bytes,
                                  long long* key_bytes_cached);
 
+/* Diagnostics of the execution plan built at create_fhe_gpu_task (used by this repository's host-side tests):
+ * out8 = {compute nodes incl. bridge nodes, data nodes, host units, LOAD units, STORE units, GPU units, nodes fused away,
+ * independent DAG components}; returns 0. */
+int lsb_gpu_task_describe(fhe_task_handle handle, long long* out8);
+/* component -> device slot for a run over `n_slots` devices (longest-processing-time-first); writes at most `capacity`
+ * entries, returns the number of components. */
+int lsb_gpu_task_shard_preview(fhe_task_handle handle, int n_slots, int* slot_of_component, int capacity);
+
 /* Copy helper for plug-in EXPORT / IMPORT executors: memcpy semantics, streaming (non-temporal) stores for large aligned
  * blocks.  Limbs handed out by alloc_component while an EXPORT executor runs are pinned staging memory that the CPU never
  * reads again; filling them with this instead of memcpy removes the read-for-ownership traffic (a third of the copy). */
